@@ -1,0 +1,66 @@
+//! Raw `extern "C"` declarations, one per symbol of include/wq4.h.
+#![allow(non_camel_case_types)]
+use std::os::raw::{c_char, c_void};
+
+#[repr(C)]
+pub struct wq4_tensor {
+    _private: [u8; 0],
+}
+#[repr(C)]
+pub struct wq4_conv1d {
+    _private: [u8; 0],
+}
+pub type wq4_stream = *mut c_void;
+
+pub const WQ4_OK: i32 = 0;
+pub const WQ4_EPI_GELU: u32 = 1;
+pub const WQ4_OPERANDS_BF16: u32 = 16;
+pub const WQ4_FORCE_GEMM: u32 = 32;
+pub const WQ4_FORCE_GEMV: u32 = 64;
+
+extern "C" {
+    pub fn wq4_last_error() -> *const c_char;
+    pub fn wq4_version() -> i32;
+    pub fn wq4_device_count() -> i32;
+
+    pub fn wq4_tensor_create(host_blocks: *const u8, nbytes: usize, n: i64, k: i64, device: i32,
+                             stream: wq4_stream, out: *mut *mut wq4_tensor) -> i32;
+    pub fn wq4_tensor_destroy(t: *mut wq4_tensor) -> i32;
+    pub fn wq4_tensor_shape(t: *const wq4_tensor, n: *mut i64, k: *mut i64) -> i32;
+    pub fn wq4_tensor_num_blocks(t: *const wq4_tensor) -> i64;
+    pub fn wq4_tensor_device(t: *const wq4_tensor) -> i32;
+    pub fn wq4_tensor_device_bytes(t: *const wq4_tensor) -> usize;
+    pub fn wq4_tensor_dequantize(t: *const wq4_tensor, dst_dev: *mut f32, stream: wq4_stream) -> i32;
+    pub fn wq4_tensor_export_gguf(t: *const wq4_tensor, dst_dev: *mut u8, stream: wq4_stream) -> i32;
+
+    pub fn wq4_linear_workspace_bytes(w: *const wq4_tensor, b: i64, m: i64) -> usize;
+    pub fn wq4_matmul(w: *const wq4_tensor, x_dev: *const f32, y_dev: *mut f32, b: i64, m: i64,
+                      workspace_dev: *mut c_void, workspace_bytes: usize, stream: wq4_stream) -> i32;
+    pub fn wq4_linear_forward(w: *const wq4_tensor, bias_dev: *const f32, x_dev: *const f32,
+                              y_dev: *mut f32, b: i64, m: i64, workspace_dev: *mut c_void,
+                              workspace_bytes: usize, stream: wq4_stream) -> i32;
+    pub fn wq4_linear_forward_ex(w: *const wq4_tensor, bias_dev: *const f32, x_f32_dev: *const f32,
+                                 x_f16_dev: *const c_void, y_f32_dev: *mut f32, y_f16_dev: *mut c_void,
+                                 residual_dev: *const f32, rows: i64, flags: u32,
+                                 workspace_dev: *mut c_void, workspace_bytes: usize,
+                                 stream: wq4_stream) -> i32;
+
+    pub fn wq4_ffn_workspace_bytes(fc1: *const wq4_tensor, fc2: *const wq4_tensor, b: i64, m: i64) -> usize;
+    pub fn wq4_ffn_forward(fc1: *const wq4_tensor, b1_dev: *const f32, fc2: *const wq4_tensor,
+                           b2_dev: *const f32, x_dev: *const f32, y_dev: *mut f32, b: i64, m: i64,
+                           workspace_dev: *mut c_void, workspace_bytes: usize, stream: wq4_stream) -> i32;
+
+    pub fn wq4_conv1d_create(host_w: *const f32, host_bias: *const f32, c_out: i64, c_in: i64,
+                             ksize: i64, device: i32, stream: wq4_stream,
+                             out: *mut *mut wq4_conv1d) -> i32;
+    pub fn wq4_conv1d_destroy(c: *mut wq4_conv1d) -> i32;
+    pub fn wq4_conv1d_workspace_bytes(c: *const wq4_conv1d, b: i64, t: i64, padding: i64, stride: i64) -> usize;
+    pub fn wq4_conv1d_forward(c: *const wq4_conv1d, x_dev: *const f32, y_dev: *mut f32, b: i64, t: i64,
+                              padding: i64, stride: i64, flags: u32, workspace_dev: *mut c_void,
+                              workspace_bytes: usize, stream: wq4_stream) -> i32;
+
+    pub fn wq4_linear_plan(w: *const wq4_tensor, rows: i64, flags: u32, tile_m: *mut i32) -> i32;
+    pub fn wq4_launch_count() -> i64;
+    pub fn wq4_launch_count_reset();
+    pub fn wq4_device_error_flag(device: i32) -> i32;
+}

@@ -1,0 +1,149 @@
+/*
+ * wq4.h -- C ABI of the B200 (sm_100a) Q4_0 hot path of whisper-burn.
+ *
+ * Every entry point replaces one reference interface (file:line under the reference tree):
+ *
+ *   wq4_tensor_create        Q4Tensor::from_q4_bytes          src/gguf/tensor.rs:35-71
+ *   wq4_tensor_shape         Q4Tensor::shape                  src/gguf/tensor.rs:74
+ *   wq4_tensor_num_blocks    Q4Tensor::num_blocks             src/gguf/tensor.rs:79
+ *   wq4_tensor_dequantize    Q4Tensor::dequantize             src/gguf/tensor.rs:88-113
+ *   wq4_matmul               q4_matmul                        src/gguf/op.rs:47-116 (+ shader.wgsl:51-92)
+ *   wq4_linear_forward       Q4Linear::forward                src/gguf/linear.rs:34-40
+ *   wq4_ffn_forward          Q4FFN::forward (+ gelu)          src/model/layers.rs:35-41,54-58
+ *   wq4_conv1d_create/forward Conv1D::new / Conv1D::forward   src/model/layers.rs:69-132
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, int32_t status (0 = WQ4_OK).  Nothing aborts or
+ *     throws across this boundary; wq4_last_error() returns a thread-local message.
+ *   - *_dev pointers are device pointers on the device the weight object was created on;
+ *     activations, biases and outputs are contiguous row-major f32 exactly as in the
+ *     reference ([B,M,K] -> [B,M,N]).  Weights enter as raw GGUF Q4_0 bytes (18-byte blocks,
+ *     f16 scale + 16 nibble bytes) in HOST memory and are repacked once on the device.
+ *   - Stream ordered: every call only enqueues work on `stream` (a cudaStream_t passed as
+ *     void*); no hidden synchronisation, no allocation inside forward calls, CUDA-graph
+ *     capturable.  The caller owns activation/output/workspace buffers; the library owns the
+ *     repacked weight storage inside wq4_tensor / wq4_conv1d.
+ *   - There is no CPU fallback: without a CUDA device every compute entry point returns
+ *     WQ4_ERR_CUDA.
+ */
+#ifndef WQ4_H
+#define WQ4_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define WQ4_API __declspec(dllexport)
+#else
+#define WQ4_API __attribute__((visibility("default")))
+#endif
+
+typedef struct wq4_tensor wq4_tensor;   /* device-resident Q4_0 weight [N,K]            */
+typedef struct wq4_conv1d wq4_conv1d;   /* device-resident Conv1D weight + bias          */
+typedef void *wq4_stream;               /* cudaStream_t                                  */
+
+enum {
+    WQ4_OK = 0,
+    WQ4_ERR_INVALID = 1,     /* null pointer / negative size / bad flag                   */
+    WQ4_ERR_SHAPE = 2,       /* n*k % 32 != 0 (tensor.rs:38-41), K mismatch (op.rs:58-61) */
+    WQ4_ERR_BYTES = 3,       /* byte count != n*k/32*18 (tensor.rs:44-48)                 */
+    WQ4_ERR_CUDA = 4,        /* CUDA runtime/driver error, or no device                   */
+    WQ4_ERR_UNSUPPORTED = 5, /* e.g. matmul on a tensor whose K is not a multiple of 32   */
+    WQ4_ERR_WORKSPACE = 6    /* workspace too small                                       */
+};
+
+/* Epilogue / precision flags for the *_ex entry points. */
+enum {
+    WQ4_EPI_NONE = 0,
+    WQ4_EPI_GELU = 1,        /* tanh-GELU of src/model/layers.rs:35-41 applied after bias  */
+    WQ4_OPERANDS_BF16 = 16,  /* tensor-core operands in bf16 instead of the default f16    */
+    WQ4_FORCE_GEMM = 32,     /* use the tcgen05 GEMM kernel even for tiny M                */
+    WQ4_FORCE_GEMV = 64      /* use the CUDA-core GEMV kernel (M <= 8 only)                */
+};
+
+WQ4_API const char *wq4_last_error(void);
+WQ4_API int32_t wq4_version(void);
+/* Number of CUDA devices visible (0 when there is no GPU / driver). */
+WQ4_API int32_t wq4_device_count(void);
+
+/* ---- Q4Tensor ------------------------------------------------------------------------ */
+/* host_blocks: nbytes of raw GGUF Q4_0 data for a [n,k] weight (row-major, blocks of 32
+ * consecutive elements).  Validates exactly as tensor.rs:38-48, uploads and repacks. */
+WQ4_API int32_t wq4_tensor_create(const uint8_t *host_blocks, size_t nbytes, int64_t n, int64_t k,
+                                  int32_t device, wq4_stream stream, wq4_tensor **out);
+WQ4_API int32_t wq4_tensor_destroy(wq4_tensor *t);
+WQ4_API int32_t wq4_tensor_shape(const wq4_tensor *t, int64_t *n, int64_t *k);
+WQ4_API int64_t wq4_tensor_num_blocks(const wq4_tensor *t);
+WQ4_API int32_t wq4_tensor_device(const wq4_tensor *t);
+/* Bytes of device memory held by the repacked weight (scales + nibbles + padding). */
+WQ4_API size_t wq4_tensor_device_bytes(const wq4_tensor *t);
+/* dst_dev: n*k floats, row-major [n,k]; bit-identical to Q4Tensor::dequantize. */
+WQ4_API int32_t wq4_tensor_dequantize(const wq4_tensor *t, float *dst_dev, wq4_stream stream);
+/* Inverse of the upload repack: writes the original n*k/32*18 GGUF bytes to dst_dev. */
+WQ4_API int32_t wq4_tensor_export_gguf(const wq4_tensor *t, uint8_t *dst_dev, wq4_stream stream);
+
+/* ---- q4_matmul / Q4Linear ------------------------------------------------------------ */
+/* Workspace (bytes) wq4_matmul / wq4_linear_forward need for a [b,m,K] input. */
+WQ4_API size_t wq4_linear_workspace_bytes(const wq4_tensor *w, int64_t b, int64_t m);
+/* y[b,m,N] = x[b,m,K] . W[N,K]^T            (q4_matmul, op.rs:47) */
+WQ4_API int32_t wq4_matmul(const wq4_tensor *w, const float *x_dev, float *y_dev, int64_t b,
+                           int64_t m, void *workspace_dev, size_t workspace_bytes,
+                           wq4_stream stream);
+/* y = x . W^T + bias (bias_dev may be NULL)  (Q4Linear::forward, linear.rs:34-40) */
+WQ4_API int32_t wq4_linear_forward(const wq4_tensor *w, const float *bias_dev, const float *x_dev,
+                                   float *y_dev, int64_t b, int64_t m, void *workspace_dev,
+                                   size_t workspace_bytes, wq4_stream stream);
+/* Extended form used by the fused callers.  rows = b*m.
+ *   x_f32_dev / x_f16_dev : exactly one non-NULL ([rows,K]; f16/bf16 per flags)
+ *   y_f32_dev / y_f16_dev : at least one non-NULL ([rows,N])
+ *   residual_dev          : optional f32 [rows,N] added after bias/GELU
+ *   flags                 : WQ4_EPI_* | WQ4_OPERANDS_BF16 | WQ4_FORCE_* */
+WQ4_API int32_t wq4_linear_forward_ex(const wq4_tensor *w, const float *bias_dev,
+                                      const float *x_f32_dev, const void *x_f16_dev,
+                                      float *y_f32_dev, void *y_f16_dev, const float *residual_dev,
+                                      int64_t rows, uint32_t flags, void *workspace_dev,
+                                      size_t workspace_bytes, wq4_stream stream);
+
+/* ---- Q4FFN ---------------------------------------------------------------------------- */
+WQ4_API size_t wq4_ffn_workspace_bytes(const wq4_tensor *fc1, const wq4_tensor *fc2, int64_t b,
+                                       int64_t m);
+/* y = fc2(gelu(fc1(x)))  (layers.rs:54-58); biases may be NULL. */
+WQ4_API int32_t wq4_ffn_forward(const wq4_tensor *fc1, const float *b1_dev, const wq4_tensor *fc2,
+                                const float *b2_dev, const float *x_dev, float *y_dev, int64_t b,
+                                int64_t m, void *workspace_dev, size_t workspace_bytes,
+                                wq4_stream stream);
+
+/* ---- Conv1D --------------------------------------------------------------------------- */
+/* host_w: [c_out, c_in, ksize] f32 (loader.rs:256-281); host_bias: [c_out] f32. */
+WQ4_API int32_t wq4_conv1d_create(const float *host_w, const float *host_bias, int64_t c_out,
+                                  int64_t c_in, int64_t ksize, int32_t device, wq4_stream stream,
+                                  wq4_conv1d **out);
+WQ4_API int32_t wq4_conv1d_destroy(wq4_conv1d *c);
+WQ4_API size_t wq4_conv1d_workspace_bytes(const wq4_conv1d *c, int64_t b, int64_t t,
+                                          int64_t padding, int64_t stride);
+/* x [b,c_in,t] -> y [b,c_out,t_out], t_out = (t + 2*padding - ksize)/stride + 1
+ * (layers.rs:77-132).  flags: WQ4_EPI_GELU fuses the GELU that encoder.rs:90,94 applies. */
+WQ4_API int32_t wq4_conv1d_forward(const wq4_conv1d *c, const float *x_dev, float *y_dev,
+                                   int64_t b, int64_t t, int64_t padding, int64_t stride,
+                                   uint32_t flags, void *workspace_dev, size_t workspace_bytes,
+                                   wq4_stream stream);
+
+/* ---- Introspection used by bench.py / tests ------------------------------------------- */
+/* Which kernel family a [rows,K]x[N,K]^T call dispatches to: 0 = GEMV (CUDA cores),
+ * 1 = tcgen05 GEMM.  `tile_m` receives the GEMM row tile (0 for GEMV). */
+WQ4_API int32_t wq4_linear_plan(const wq4_tensor *w, int64_t rows, uint32_t flags,
+                                int32_t *tile_m);
+/* Count of kernels this library has launched on the calling thread since the last reset. */
+WQ4_API int64_t wq4_launch_count(void);
+WQ4_API void wq4_launch_count_reset(void);
+/* Sticky device-side error flag set by kernels (pipeline wait timeouts); 0 = clean. */
+WQ4_API int32_t wq4_device_error_flag(int32_t device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WQ4_H */

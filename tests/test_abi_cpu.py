@@ -1,0 +1,83 @@
+"""CPU-only checks of the drop-in boundary: the C-ABI library builds/loads, exports every symbol
+include/wq4.h declares, validates arguments like the reference (tensor.rs:38-48, op.rs:53-61) and
+fails loudly -- never falls back -- without a GPU."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import whisper_burn_b200 as wb
+from whisper_burn_b200 import _lib
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _declared_symbols():
+    text = (ROOT / "include" / "wq4.h").read_text()
+    return sorted(set(re.findall(r"WQ4_API[^;]*?\b(wq4_[a-z0-9_]+)\s*\(", text, flags=re.S)))
+
+
+def test_library_exports_every_declared_symbol():
+    L = wb.lib()
+    syms = _declared_symbols()
+    assert len(syms) >= 25
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/wq4.h but not exported by libwq4.so"
+    assert L.wq4_version() >= 100
+
+
+def test_header_cites_reference_interfaces():
+    text = (ROOT / "include" / "wq4.h").read_text()
+    for cite in ("src/gguf/tensor.rs:35", "src/gguf/op.rs:47", "src/gguf/linear.rs:34",
+                 "src/model/layers.rs:35", "src/model/layers.rs:69"):
+        assert cite in text
+
+
+def test_rust_ffi_declares_same_symbols():
+    rs = (ROOT / "ffi" / "src" / "sys.rs").read_text()
+    for s in _declared_symbols():
+        assert re.search(rf"\bfn {s}\b", rs), f"{s} missing from ffi/src/sys.rs"
+
+
+def test_tensor_create_validation_matches_reference():
+    ok = np.zeros(18, np.uint8)
+    with pytest.raises(wb.Wq4Error) as e:   # tensor.rs:38-41
+        wb.Q4Tensor.from_q4_bytes(ok, [1, 31], "cuda:0")
+    assert e.value.status == 2 and "divisible by 32" in e.value.message
+    with pytest.raises(wb.Wq4Error) as e:   # tensor.rs:44-48
+        wb.Q4Tensor.from_q4_bytes(np.zeros(17, np.uint8), [1, 32], "cuda:0")
+    assert e.value.status == 3 and "byte count mismatch" in e.value.message
+    with pytest.raises(wb.Wq4Error):
+        wb.Q4Tensor.from_q4_bytes(ok, [1, 32], "cpu")
+
+
+def test_no_cpu_fallback_without_gpu():
+    L = wb.lib()
+    if L.wq4_device_count() > 0:
+        pytest.skip("GPU present")
+    with pytest.raises(wb.Wq4Error) as e:
+        wb.Q4Tensor.from_q4_bytes(np.zeros(18, np.uint8), [1, 32], "cuda:0")
+    assert e.value.status == 4 and "no CPU fallback" in e.value.message
+    with pytest.raises(wb.Wq4Error):
+        wb.Conv1D(np.zeros((4, 3, 3), np.float32), np.zeros(4, np.float32), device="cuda:0")
+
+
+def test_null_arguments_are_errors_not_crashes():
+    L = wb.lib()
+    assert L.wq4_tensor_create(None, 18, 1, 32, 0, None, None) == 1
+    n, k = C.c_int64(), C.c_int64()
+    assert L.wq4_tensor_shape(None, C.byref(n), C.byref(k)) == 1
+    assert L.wq4_tensor_num_blocks(None) == -1
+    assert L.wq4_tensor_dequantize(None, None, None) == 1
+    assert L.wq4_linear_forward(None, None, None, None, 1, 1, None, 0, None) == 1
+    assert L.wq4_tensor_destroy(None) == 0
+    assert L.wq4_conv1d_destroy(None) == 0
+    assert b"null" in L.wq4_last_error() or len(L.wq4_last_error()) > 0
+
+
+def test_product_package_does_not_import_oracle():
+    for f in (ROOT / "whisper_burn_b200").rglob("*"):
+        if f.suffix in (".py", ".cu", ".cuh", ".cpp", ".h", ".sh"):
+            assert "oracle" not in f.read_text().lower().replace("test oracle", ""), f
