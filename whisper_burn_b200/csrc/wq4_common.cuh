@@ -105,6 +105,7 @@ struct LinearArgs {
 int32_t wq4_launch_gemv(const LinearArgs &a);
 int32_t wq4_launch_gemm_q4(const LinearArgs &a, int tile_m);
 int wq4_pick_tile_m(int64_t rows, int64_t np);
+int wq4_gemm_cluster_size(int64_t np);
 
 // Tensor-core GEMM on a dense 16-bit weight (the Conv1D stem).  The activation operand is a
 // strided 3-D view [x_batch][x_rows][x_k] (element strides x_batch_stride / x_row_stride / 1), which

@@ -15,15 +15,22 @@
 //   warp 2      raw producer   cp.async.bulk of the raw Q4 slab (4 KiB nibbles + 512 B scales / stage)
 //   warp 3      TMEM allocator
 //   warps 4-11  dequantisers   nibbles -> f16 (lop3 magic 0x6400, exact (nib-8), one rounding in
-//                              the product with the f16 scale) -> 128B-swizzled K-major A tile
+//                              the product with the f16 scale) -> 128B-swizzled K-major A tile;
+//                              4 groups x 2 warps, group g owns ring slot g (4 stages in flight)
 //   warps 12-15 epilogue       tcgen05.ld -> +bias -> GELU -> +residual -> f32 / f16 stores
 // Pipelines: raw ring (6 stages) -> A/X ring (4 stages, mbarrier full/empty) -> double-buffered
 // TMEM accumulator (full/empty) so the epilogue of tile i overlaps the main loop of tile i+1.
+//
+// CTA pairs: the kernel is launched as clusters of 2 CTAs that work on the same activation tile and
+// on neighbouring weight panels.  Each CTA TMA-loads half of the X tile and multicasts it into both
+// CTAs' shared memory, which halves the L2->SM traffic of the dominant operand (at 128x256 tiles a
+// lone CTA needs 36.6 KB per 512 tensor-pipe cycles, more than the L2 can deliver to 148 SMs).
 //
 // Roofline: tensor cores.  Algorithmic work = 2*rows*N*K flop per launch.
 #include <cuda.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "wq4_common.cuh"
 #include "wq4_ptx.cuh"
@@ -32,7 +39,7 @@ namespace {
 
 using namespace ptx;
 
-constexpr int kStages = 4;
+constexpr int kStages = 4;   // == number of dequant groups (group g owns slot g)
 constexpr int kRawStages = 6;
 constexpr int kThreads = 512;
 constexpr int kBK = 64;                                 // K elements per stage
@@ -41,6 +48,7 @@ constexpr int kRawNibBytes = 2 * WQ4_PANEL_ROWS * 16;   // 4 KiB
 constexpr int kRawSclBytes = 2 * WQ4_PANEL_ROWS * 2;    // 512 B
 constexpr int kRawStageBytes = kRawNibBytes + kRawSclBytes;
 constexpr int kNumDequantThreads = 256;
+constexpr int kDequantGroupThreads = 64;   // 4 groups, one per A-ring slot
 constexpr int kNumEpilogueThreads = 128;
 
 template <int TILE_M>
@@ -80,6 +88,14 @@ struct GemmParams {
     int *dev_err;
 };
 
+// (a & b) | c in one LOP3 (immLut 0xEA); b and c live in registers across the loop.
+__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 template <bool kBF16>
 __device__ __forceinline__ uint4 dequant_word(uint32_t w, uint32_t d2)
 {
@@ -89,11 +105,11 @@ __device__ __forceinline__ uint4 dequant_word(uint32_t w, uint32_t d2)
         const __half2 k16th = __floats2half2_rn(0.0625f, 0.0625f);
         const __half2 km72 = __floats2half2_rn(-72.0f, -72.0f);
         const __half2 d = *reinterpret_cast<const __half2 *>(&d2);
-        uint32_t t0 = (w & 0x000F000Fu) | 0x64006400u;
-        uint32_t t1 = (w & 0x00F000F0u) | 0x64006400u;
+        uint32_t t0 = lop3_and_or(w, 0x000F000Fu, 0x64006400u);
+        uint32_t t1 = lop3_and_or(w, 0x00F000F0u, 0x64006400u);
         uint32_t w8 = w >> 8;
-        uint32_t t2 = (w8 & 0x000F000Fu) | 0x64006400u;
-        uint32_t t3 = (w8 & 0x00F000F0u) | 0x64006400u;
+        uint32_t t2 = lop3_and_or(w8, 0x000F000Fu, 0x64006400u);
+        uint32_t t3 = lop3_and_or(w8, 0x00F000F0u, 0x64006400u);
         __half2 q0 = __hmul2(__hsub2(*reinterpret_cast<__half2 *>(&t0), k1032), d);
         __half2 q1 = __hmul2(__hfma2(*reinterpret_cast<__half2 *>(&t1), k16th, km72), d);
         __half2 q2 = __hmul2(__hsub2(*reinterpret_cast<__half2 *>(&t2), k1032), d);
@@ -106,10 +122,10 @@ __device__ __forceinline__ uint4 dequant_word(uint32_t w, uint32_t d2)
         // bf16 has 8 significant bits: 128 + nib is exact, 128 + 16*nib is not -> shift first.
         const __nv_bfloat162 k136 = __floats2bfloat162_rn(136.0f, 136.0f);
         const __nv_bfloat162 d = *reinterpret_cast<const __nv_bfloat162 *>(&d2);
-        uint32_t t0 = (w & 0x000F000Fu) | 0x43004300u;
-        uint32_t t1 = ((w >> 4) & 0x000F000Fu) | 0x43004300u;
-        uint32_t t2 = ((w >> 8) & 0x000F000Fu) | 0x43004300u;
-        uint32_t t3 = ((w >> 12) & 0x000F000Fu) | 0x43004300u;
+        uint32_t t0 = lop3_and_or(w, 0x000F000Fu, 0x43004300u);
+        uint32_t t1 = lop3_and_or(w >> 4, 0x000F000Fu, 0x43004300u);
+        uint32_t t2 = lop3_and_or(w >> 8, 0x000F000Fu, 0x43004300u);
+        uint32_t t3 = lop3_and_or(w >> 12, 0x000F000Fu, 0x43004300u);
         __nv_bfloat162 q0 = __hmul2(__hsub2(*reinterpret_cast<__nv_bfloat162 *>(&t0), k136), d);
         __nv_bfloat162 q1 = __hmul2(__hsub2(*reinterpret_cast<__nv_bfloat162 *>(&t1), k136), d);
         __nv_bfloat162 q2 = __hmul2(__hsub2(*reinterpret_cast<__nv_bfloat162 *>(&t2), k136), d);
@@ -148,17 +164,22 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     constexpr uint32_t kTmemCols = 2 * TILE_M;   // 64..512, power of two
-    const int num_tiles = p.np * p.mt_per_b * p.nbatch;
+    const int csize = (int)cluster_nctarank();   // 1 or 2 CTAs share each activation tile
+    const int crank = (int)cluster_ctarank();
+    const int npc = p.np / csize;                // panel groups (np is even when csize == 2)
+    const int num_tiles = npc * p.mt_per_b * p.nbatch;      // tiles per cluster-slot
+    const int slot = (int)blockIdx.x / csize;               // this CTA's cluster index
+    const int nslots = (int)gridDim.x / csize;
 
     if (threadIdx.x == 0) {
         *cta_abort = 0;
         for (int s = 0; s < kStages; s++) {
-            mbar_init(bar_full(s), kDenseA ? 1u : 1u + kNumDequantThreads);
-            mbar_init(bar_empty(s), 1u);
+            mbar_init(bar_full(s), kDenseA ? 1u : 1u + kDequantGroupThreads);
+            mbar_init(bar_empty(s), (uint32_t)csize);
         }
         for (int s = 0; s < kRawStages; s++) {
             mbar_init(bar_raw_full(s), 1u);
-            mbar_init(bar_raw_empty(s), kNumDequantThreads);
+            mbar_init(bar_raw_empty(s), kDequantGroupThreads);
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(bar_acc_full(b), 1u);
@@ -174,13 +195,14 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     }
     tc_fence_before();
     __syncthreads();
+    if (csize > 1) cluster_sync_all();   // peer barriers must exist before any multicast lands
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
 
     // tile -> (batch, m tile, weight panel); consecutive tiles share the activation tile
     auto decode_tile = [&](int tile, int &b, int &t0, int &panel) {
-        panel = tile % p.np;
-        int mt = tile / p.np;
+        panel = (tile % npc) * csize + crank;
+        int mt = tile / npc;
         b = mt / p.mt_per_b;
         t0 = (mt - b * p.mt_per_b) * TILE_M;
     };
@@ -189,7 +211,7 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         // ============================ X (and dense A) TMA producer ============================
         if (lane == 0) {
             uint32_t c = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = slot; tile < num_tiles; tile += nslots) {
                 int b, t0, panel;
                 decode_tile(tile, b, t0, panel);
                 for (int ks = 0; ks < p.kst; ks++, c++) {
@@ -197,7 +219,13 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                     const uint32_t ph = (c / kStages) & 1u;
                     mbar_wait(bar_empty(s), ph ^ 1u, cta_abort, p.dev_err, 101);
                     mbar_arrive_expect_tx(bar_full(s), L::x_stage + (kDenseA ? kAStageBytes : 0));
-                    tma_load_3d(x_smem + s * L::x_stage, &tm_x, bar_full(s), ks * kBK, t0, b);
+                    if (csize == 1) {
+                        tma_load_3d(x_smem + s * L::x_stage, &tm_x, bar_full(s), ks * kBK, t0, b);
+                    } else {
+                        // my half of the rows, delivered to both CTAs of the pair
+                        tma_load_3d_mcast(x_smem + s * L::x_stage + crank * (L::x_stage / 2), &tm_x, bar_full(s),
+                                          ks * kBK, t0 + crank * (TILE_M / 2), b, (uint16_t)0x3);
+                    }
                     if (kDenseA) tma_load_2d(a_smem + s * kAStageBytes, &tm_a, bar_full(s), ks * kBK, panel * WQ4_PANEL_ROWS);
                 }
             }
@@ -207,7 +235,7 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_f16(128, TILE_M, kBF16);
             uint32_t c = 0, it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, it++) {
+            for (int tile = slot; tile < num_tiles; tile += nslots, it++) {
                 const uint32_t ab = it & 1u;
                 const uint32_t aph = (it >> 1) & 1u;
                 mbar_wait(bar_acc_empty(ab), aph ^ 1u, cta_abort, p.dev_err, 102);
@@ -225,7 +253,10 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                         // +32 bytes (16 K elements) inside the 128-byte swizzle atom: +2 in >>4 units
                         umma_f16(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ks | k) != 0 ? 1u : 0u);
                     }
-                    umma_commit(bar_empty(s));          // frees the A/X slot when these MMAs retire
+                    // frees the A/X slot when these MMAs retire (in both CTAs: the peer's producer
+                    // multicasts into this CTA's slot as well)
+                    if (csize == 1) umma_commit(bar_empty(s));
+                    else umma_commit_mcast(bar_empty(s), (uint16_t)0x3);
                 }
                 umma_commit(bar_acc_full(ab));          // accumulator ready for the epilogue
             }
@@ -234,7 +265,7 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         // ================================= raw Q4 slab producer ================================
         if (!kDenseA && lane == 0) {
             uint32_t c = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = slot; tile < num_tiles; tile += nslots) {
                 int b, t0, panel;
                 decode_tile(tile, b, t0, panel);
                 const size_t panel_entry = (size_t)panel * p.kbp * WQ4_PANEL_ROWS;
@@ -252,52 +283,70 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         }
     } else if (warp >= 4 && warp < 12) {
         // ===================================== dequantisers ====================================
+        // Four groups of two warps; group g owns ring slot g, so four K-stages are dequantised
+        // concurrently (the per-stage chain wait -> LDS -> ALU -> STS -> fence -> arrive is latency
+        // bound; running it four-wide is what keeps the tensor pipe fed).
         if (!kDenseA) {
-            const int t = threadIdx.x - 128;       // 0..255
-            const int r = t & 127;                 // weight row inside the panel
-            const int h = t >> 7;                  // which of the stage's two Q4 blocks
-            uint32_t c = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                for (int ks = 0; ks < p.kst; ks++, c++) {
-                    const int rs = c % kRawStages;
-                    const uint32_t rph = (c / kRawStages) & 1u;
-                    const int s = c % kStages;
-                    const uint32_t ph = (c / kStages) & 1u;
-                    mbar_wait(bar_raw_full(rs), rph, cta_abort, p.dev_err, 105);
-                    const uint8_t *raw = base_ptr + L::raw_off + rs * kRawStageBytes;
-                    const uint4 q = *reinterpret_cast<const uint4 *>(raw + (h * 128 + r) * 16);
-                    const uint16_t sb = *reinterpret_cast<const uint16_t *>(raw + kRawNibBytes + (h * 128 + r) * 2);
-                    mbar_arrive(bar_raw_empty(rs));      // raw slot may be refilled
-                    uint32_t d2;
+            const int g = (warp - 4) >> 1;                       // 0..3 == A-ring slot
+            const int t64 = threadIdx.x - 128 - g * kDequantGroupThreads;   // 0..63
+            const int my_tiles = (num_tiles - slot + nslots - 1) / nslots;
+            const uint32_t total = (uint32_t)my_tiles * (uint32_t)p.kst;
+            uint8_t *a_slot = base_ptr + L::a_off + g * kAStageBytes;
+            for (uint32_t c = g; c < total; c += kStages) {
+                const int rs = c % kRawStages;
+                const uint32_t rph = (c / kRawStages) & 1u;
+                const uint32_t ph = (c / kStages) & 1u;
+                mbar_wait(bar_raw_full(rs), rph, cta_abort, p.dev_err, 105);
+                const uint8_t *raw = base_ptr + L::raw_off + rs * kRawStageBytes;
+                uint4 q[4];
+                uint32_t d2[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {                    // task j: rows (j&1)*64 + t64, block j>>1
+                    const int e = (j >> 1) * 128 + (j & 1) * 64 + t64;
+                    q[j] = *reinterpret_cast<const uint4 *>(raw + e * 16);
+                    const uint16_t sb = *reinterpret_cast<const uint16_t *>(raw + kRawNibBytes + e * 2);
                     if constexpr (!kBF16) {
-                        d2 = (uint32_t)sb | ((uint32_t)sb << 16);
+                        d2[j] = (uint32_t)sb | ((uint32_t)sb << 16);
                     } else {
                         __nv_bfloat16 db = __float2bfloat16_rn(__half2float(__ushort_as_half(sb)));
                         uint16_t bb = *reinterpret_cast<uint16_t *>(&db);
-                        d2 = (uint32_t)bb | ((uint32_t)bb << 16);
+                        d2[j] = (uint32_t)bb | ((uint32_t)bb << 16);
                     }
-                    const uint4 c0 = dequant_word<kBF16>(q.x, d2);
-                    const uint4 c1 = dequant_word<kBF16>(q.y, d2);
-                    const uint4 c2 = dequant_word<kBF16>(q.z, d2);
-                    const uint4 c3 = dequant_word<kBF16>(q.w, d2);
-                    mbar_wait(bar_empty(s), ph ^ 1u, cta_abort, p.dev_err, 106);
-                    // row r of the K-major tile: 128 bytes, 16-byte chunk j stored at j ^ (r & 7)
-                    uint8_t *row = base_ptr + L::a_off + s * kAStageBytes + r * 128;
-                    const int x7 = r & 7;
-                    *reinterpret_cast<uint4 *>(row + (((4 * h + 0) ^ x7) << 4)) = c0;
-                    *reinterpret_cast<uint4 *>(row + (((4 * h + 1) ^ x7) << 4)) = c1;
-                    *reinterpret_cast<uint4 *>(row + (((4 * h + 2) ^ x7) << 4)) = c2;
-                    *reinterpret_cast<uint4 *>(row + (((4 * h + 3) ^ x7) << 4)) = c3;
-                    fence_proxy_async_smem();            // generic-proxy writes -> visible to tcgen05
-                    mbar_arrive(bar_full(s));
                 }
+                mbar_arrive(bar_raw_empty(rs));                  // raw slot may be refilled
+                mbar_wait(bar_empty(g), ph ^ 1u, cta_abort, p.dev_err, 106);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int r = (j & 1) * 64 + t64;
+                    const int h = j >> 1;
+                    // row r of the K-major tile: 128 bytes, 16-byte chunk i stored at i ^ (r & 7)
+                    uint8_t *row = a_slot + r * 128;
+                    const int x7 = r & 7;
+                    *reinterpret_cast<uint4 *>(row + (((4 * h + 0) ^ x7) << 4)) = dequant_word<kBF16>(q[j].x, d2[j]);
+                    *reinterpret_cast<uint4 *>(row + (((4 * h + 1) ^ x7) << 4)) = dequant_word<kBF16>(q[j].y, d2[j]);
+                    *reinterpret_cast<uint4 *>(row + (((4 * h + 2) ^ x7) << 4)) = dequant_word<kBF16>(q[j].z, d2[j]);
+                    *reinterpret_cast<uint4 *>(row + (((4 * h + 3) ^ x7) << 4)) = dequant_word<kBF16>(q[j].w, d2[j]);
+                }
+                fence_proxy_async_smem();                        // generic-proxy writes -> visible to tcgen05
+                mbar_arrive(bar_full(g));
             }
         }
     } else if (warp >= 12) {
         // ======================================= epilogue =======================================
         const int q = warp & 3;                    // TMEM lane quarter this warp may access
+        // The flag combination is warp-uniform and fixed for the launch: pick a specialised
+        // straight-line body once (no per-element branches), generic body as the fallback.
+        const bool f_gelu = (p.flags & WQ4_EPI_GELU) != 0, f_res = p.residual != nullptr;
+        const bool f_y32 = p.y32 != nullptr, f_y16 = p.y16 != nullptr;
+        int mode = 7;
+        if (!f_gelu && !f_res && f_y32 && !f_y16) mode = 0;        // q4_matmul / Q4Linear drop-in
+        else if (!f_gelu && !f_res && !f_y32 && f_y16) mode = 1;   // fused QKV -> f16
+        else if (f_gelu && !f_res && !f_y32 && f_y16) mode = 2;    // fc1 / conv1 + GELU -> f16
+        else if (!f_gelu && f_res && f_y32 && !f_y16) mode = 3;    // out-proj / fc2 + residual
+        else if (f_gelu && !f_res && f_y32 && !f_y16) mode = 4;    // conv + GELU drop-in
+        else if (f_gelu && f_res && f_y32 && !f_y16) mode = 5;     // conv2 + GELU + positional emb.
         uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, it++) {
+        for (int tile = slot; tile < num_tiles; tile += nslots, it++) {
             int b, t0, panel;
             decode_tile(tile, b, t0, panel);
             const uint32_t ab = it & 1u;
@@ -315,25 +364,67 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                 uint32_t v[32];
                 tmem_ld_32x32b_x32(tmem_base + ab * TILE_M + c0 + ((uint32_t)(q * 32) << 16), v);
                 tmem_ld_wait();
-                if (n_ok) {
+                if (!n_ok) continue;
+                const int tb = t0 + c0;
+                const int nvalid = min(32, p.t_len - tb);
+                float *y32 = p.y32 ? p.y32 + obase + (long long)tb * p.ot : nullptr;
+                const float *res = p.residual ? p.residual + rbase + (long long)tb * p.ot : nullptr;
+                const long long ot = p.ot;
+                auto body = [&](auto GELU, auto RES, auto Y32, auto Y16, auto FULL) {
+                    [[maybe_unused]] auto *y16h = reinterpret_cast<__half *>(p.y16) + (Y16.value ? obase + (long long)tb * ot : 0);
+                    [[maybe_unused]] auto *y16b = reinterpret_cast<__nv_bfloat16 *>(p.y16) + (Y16.value ? obase + (long long)tb * ot : 0);
+                    [[maybe_unused]] float r[32];
+                    if constexpr (RES.value) {
+#pragma unroll
+                        for (int j = 0; j < 32; j++) r[j] = (FULL.value || j < nvalid) ? res[(long long)j * ot] : 0.0f;
+                    }
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
-                        const int t = t0 + c0 + j;
-                        if (t < p.t_len) {
+                        float val = __uint_as_float(v[j]) + bias;
+                        if constexpr (GELU.value) val = wq4_gelu_tanh(val);
+                        if constexpr (RES.value) val += r[j];
+                        if (FULL.value || j < nvalid) {
+                            if constexpr (Y32.value) y32[(long long)j * ot] = val;
+                            if constexpr (Y16.value) {
+                                if constexpr (kBF16) y16b[(long long)j * ot] = __float2bfloat16_rn(val);
+                                else y16h[(long long)j * ot] = __float2half_rn(val);
+                            }
+                        }
+                    }
+                };
+                using T_ = std::true_type;
+                using F_ = std::false_type;
+                const bool full = nvalid == 32;
+#define WQ4_EPI(G, R, A, B)                                        \
+    do {                                                           \
+        if (full) body(G{}, R{}, A{}, B{}, T_{});                  \
+        else body(G{}, R{}, A{}, B{}, F_{});                       \
+    } while (0)
+                switch (mode) {
+                case 0: WQ4_EPI(F_, F_, T_, F_); break;
+                case 1: WQ4_EPI(F_, F_, F_, T_); break;
+                case 2: WQ4_EPI(T_, F_, F_, T_); break;
+                case 3: WQ4_EPI(F_, T_, T_, F_); break;
+                case 4: WQ4_EPI(T_, F_, T_, F_); break;
+                case 5: WQ4_EPI(T_, T_, T_, F_); break;
+                default:
+                    // generic (rare flag combinations): runtime flags, per-element checks
+#pragma unroll 4
+                    for (int j = 0; j < 32; j++) {
+                        if (j < nvalid) {
                             float val = __uint_as_float(v[j]) + bias;
-                            if (p.flags & WQ4_EPI_GELU) val = wq4_gelu_tanh(val);
-                            const long long o = obase + (long long)t * p.ot;
-                            if (p.residual) val += p.residual[rbase + (long long)t * p.ot];
-                            if (p.y32) p.y32[o] = val;
-                            if (p.y16) {
-                                if constexpr (kBF16)
-                                    reinterpret_cast<__nv_bfloat16 *>(p.y16)[o] = __float2bfloat16_rn(val);
-                                else
-                                    reinterpret_cast<__half *>(p.y16)[o] = __float2half_rn(val);
+                            if (f_gelu) val = wq4_gelu_tanh(val);
+                            const long long o = obase + (long long)(tb + j) * ot;
+                            if (f_res) val += p.residual[rbase + (long long)(tb + j) * ot];
+                            if (f_y32) p.y32[o] = val;
+                            if (f_y16) {
+                                if constexpr (kBF16) reinterpret_cast<__nv_bfloat16 *>(p.y16)[o] = __float2bfloat16_rn(val);
+                                else reinterpret_cast<__half *>(p.y16)[o] = __float2half_rn(val);
                             }
                         }
                     }
                 }
+#undef WQ4_EPI
             }
             tc_fence_before();
             mbar_arrive(bar_acc_empty(ab));
@@ -342,6 +433,7 @@ q4_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
 
     tc_fence_before();
     __syncthreads();
+    if (csize > 1) cluster_sync_all();   // no CTA may exit while its peer can still signal it
     if (warp == 3) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
@@ -404,13 +496,25 @@ int32_t launch_tile(const CUtensorMap &tx, const CUtensorMap &ta, const GemmPara
     } else if (device >= 16) {
         WQ4_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::alloc));
     }
-    const int tiles = p.np * p.mt_per_b * p.nbatch;
-    int grid = wq4_sm_count(device);
+    const int csize = wq4_gemm_cluster_size(p.np);
+    const int tiles = p.np * p.mt_per_b * p.nbatch;     // CTA tiles (a pair takes two per step)
+    int grid = wq4_sm_count(device) / csize * csize;
     if (tiles < grid) grid = tiles;
     if (grid < 1) return WQ4_OK;
-    kern<<<grid, kThreads, L::alloc, stream>>>(tx, ta, p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid, 1, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = L::alloc;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)csize;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    WQ4_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, ta, p));
     wq4_count_launch();
-    WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;
 }
 
@@ -435,6 +539,18 @@ int32_t launch_any(int tile_m, bool bf16, const CUtensorMap &tx, const CUtensorM
 }
 
 }  // namespace
+
+// CTA pairs need an even number of weight panels; WQ4_GEMM_CLUSTER=1 disables pairing.
+int wq4_gemm_cluster_size(int64_t np)
+{
+    static int forced = -1;
+    if (forced < 0) {
+        const char *e = getenv("WQ4_GEMM_CLUSTER");
+        forced = e ? atoi(e) : 0;
+    }
+    if (forced == 1) return 1;
+    return (np % 2 == 0) ? 2 : 1;
+}
 
 // Row-tile heuristic.  cost = waves * (tile_m + c): per-tile time grows with the MMA work
 // (proportional to tile_m) plus a fixed part (dequantisation of the 128 x K panel, pipeline
@@ -478,8 +594,9 @@ int32_t wq4_launch_gemm_q4(const LinearArgs &a, int tile_m)
         x16 = a.workspace;
     }
     CUtensorMap tx, ta;
+    const int csize = wq4_gemm_cluster_size(w->np);
     int32_t st = make_tmap(&tx, x16, (uint64_t)w->k, (uint64_t)a.rows, 1, (uint64_t)w->k * 2,
-                           (uint64_t)w->k * 2 * (uint64_t)a.rows, (uint32_t)tile_m, bf16, 3);
+                           (uint64_t)w->k * 2 * (uint64_t)a.rows, (uint32_t)(tile_m / csize), bf16, 3);
     if (st != WQ4_OK) return st;
     ta = tx;  // unused by the Q4 variant
     GemmParams p = {};
@@ -497,8 +614,9 @@ int32_t wq4_launch_gemm_dense(const DenseGemmArgs &a, int tile_m)
 {
     const bool bf16 = (a.flags & WQ4_OPERANDS_BF16) != 0;
     CUtensorMap tx, ta;
+    const int csize = wq4_gemm_cluster_size(a.n_pad / WQ4_PANEL_ROWS);
     int32_t st = make_tmap(&tx, a.x16, (uint64_t)a.x_k, (uint64_t)a.x_rows, (uint64_t)a.x_batch,
-                           (uint64_t)a.x_row_stride * 2, (uint64_t)a.x_batch_stride * 2, (uint32_t)tile_m, bf16, 3);
+                           (uint64_t)a.x_row_stride * 2, (uint64_t)a.x_batch_stride * 2, (uint32_t)(tile_m / csize), bf16, 3);
     if (st != WQ4_OK) return st;
     st = make_tmap(&ta, a.w16, (uint64_t)a.kdim_pad, (uint64_t)a.n_pad, 1, (uint64_t)a.kdim_pad * 2, 0,
                    WQ4_PANEL_ROWS, bf16, 2);
