@@ -10,6 +10,25 @@ pub struct wq4_tensor {
 pub struct wq4_conv1d {
     _private: [u8; 0],
 }
+#[repr(C)]
+pub struct wq4_whisper {
+    _private: [u8; 0],
+}
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct wq4_whisper_config {
+    pub n_mels: i32,
+    pub n_audio_ctx: i32,
+    pub n_audio_state: i32,
+    pub n_audio_head: i32,
+    pub n_audio_layer: i32,
+    pub n_text_ctx: i32,
+    pub n_text_state: i32,
+    pub n_text_head: i32,
+    pub n_text_layer: i32,
+    pub n_vocab: i32,
+    pub n_lang: i32,
+}
 pub type wq4_stream = *mut c_void;
 
 pub const WQ4_OK: i32 = 0;
@@ -59,8 +78,35 @@ extern "C" {
                               padding: i64, stride: i64, flags: u32, workspace_dev: *mut c_void,
                               workspace_bytes: usize, stream: wq4_stream) -> i32;
 
+    pub fn wq4_gguf_probe(data: *const u8, nbytes: usize, version: *mut u32, tensor_count: *mut u64,
+                          data_offset: *mut u64) -> i32;
+    pub fn wq4_gguf_tensor_info(data: *const u8, nbytes: usize, name: *const c_char, dims4: *mut u64,
+                                ndims: *mut u32, dtype: *mut u32, abs_offset: *mut u64, byte_size: *mut u64) -> i32;
+    pub fn wq4_whisper_config_preset(name: *const c_char, cfg: *mut wq4_whisper_config) -> i32;
+    pub fn wq4_whisper_load_gguf(path: *const c_char, cfg: *const wq4_whisper_config, device: i32,
+                                 out: *mut *mut wq4_whisper) -> i32;
+    pub fn wq4_whisper_load_gguf_memory(data: *const u8, nbytes: usize, cfg: *const wq4_whisper_config,
+                                        device: i32, out: *mut *mut wq4_whisper) -> i32;
+    pub fn wq4_whisper_destroy(m: *mut wq4_whisper) -> i32;
+    pub fn wq4_whisper_reserve(m: *mut wq4_whisper, max_batch: i64) -> i32;
+    pub fn wq4_whisper_info(m: *const wq4_whisper, d_model: *mut i64, ffn: *mut i64, vocab: *mut i64,
+                            weight_bytes: *mut i64) -> i32;
+    pub fn wq4_whisper_encode(m: *mut wq4_whisper, mel_dev: *const f32, batch: i64, enc_out_dev: *mut f32,
+                              stream: wq4_stream) -> i32;
+    pub fn wq4_whisper_transcribe(m: *mut wq4_whisper, mel_dev: *const f32, batch: i64, lang_tokens: *const i32,
+                                  tokens_out: *mut i32, counts_out: *mut i32, detected_lang_out: *mut i32,
+                                  stream: wq4_stream) -> i32;
+    pub fn wq4_whisper_decoder_pass(m: *mut wq4_whisper, tokens_host: *const i32, batch: i64, q_len: i64,
+                                    emb_pos0: i64, kv_pos0: i64, recompute_cross: i32, logits_dev: *mut f32,
+                                    stream: wq4_stream) -> i32;
+    pub fn wq4_whisper_decode_step_device(m: *mut wq4_whisper, batch: i64, position: i64, kv_len: i64,
+                                          stream: wq4_stream) -> i32;
+
     pub fn wq4_linear_plan(w: *const wq4_tensor, rows: i64, flags: u32, tile_m: *mut i32) -> i32;
     pub fn wq4_launch_count() -> i64;
     pub fn wq4_launch_count_reset();
     pub fn wq4_device_error_flag(device: i32) -> i32;
+    pub fn wq4_profile_enable(on: i32);
+    pub fn wq4_profile_reset();
+    pub fn wq4_profile_read(kind: i32, launches: *mut i64, ms: *mut f64, work: *mut f64) -> i32;
 }

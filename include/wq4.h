@@ -11,6 +11,9 @@
  *   wq4_linear_forward       Q4Linear::forward                src/gguf/linear.rs:34-40
  *   wq4_ffn_forward          Q4FFN::forward (+ gelu)          src/model/layers.rs:35-41,54-58
  *   wq4_conv1d_create/forward Conv1D::new / Conv1D::forward   src/model/layers.rs:69-132
+ *   wq4_whisper_load_gguf     load_whisper_from_gguf           src/gguf/loader.rs:26-46 (+ reader.rs:98-223)
+ *   wq4_whisper_encode        WhisperModel::encode             src/model/whisper.rs:41, encoder.rs:87-115
+ *   wq4_whisper_transcribe    WhisperModel::transcribe         src/model/whisper.rs:51-128 (batched; transcribe.rs:84-87)
  *
  * Conventions
  *   - extern "C", plain pointers and sizes, int32_t status (0 = WQ4_OK).  Nothing aborts or
@@ -132,6 +135,53 @@ WQ4_API int32_t wq4_conv1d_forward(const wq4_conv1d *c, const float *x_dev, floa
                                    uint32_t flags, void *workspace_dev, size_t workspace_bytes,
                                    wq4_stream stream);
 
+/* ---- Model level: the callers of the Q4 path (SURVEY section 8f "next") -------------------------- */
+typedef struct wq4_whisper wq4_whisper;
+typedef struct wq4_whisper_config {   /* src/model/config.rs:5-28 */
+    int32_t n_mels, n_audio_ctx, n_audio_state, n_audio_head, n_audio_layer;
+    int32_t n_text_ctx, n_text_state, n_text_head, n_text_layer, n_vocab, n_lang;
+} wq4_whisper_config;
+
+/* GGUF reader probes, host only (GgufReader::{version,tensor_count,tensor_info,tensor_data},
+ * src/gguf/reader.rs:190-223).  dims4 receives the dims as stored (reversed), padded with 1. */
+WQ4_API int32_t wq4_gguf_probe(const uint8_t *data, size_t nbytes, uint32_t *version,
+                               uint64_t *tensor_count, uint64_t *data_offset);
+WQ4_API int32_t wq4_gguf_tensor_info(const uint8_t *data, size_t nbytes, const char *name,
+                                     uint64_t *dims4, uint32_t *ndims, uint32_t *dtype,
+                                     uint64_t *abs_offset, uint64_t *byte_size);
+/* "large_v3" (config.rs:32-46) or "medium" (config.rs:49-63). */
+WQ4_API int32_t wq4_whisper_config_preset(const char *name, wq4_whisper_config *cfg);
+/* GGUF v2/v3 with the reference's tensor names (loader.rs:160-377); Q4_0 linears, F32/F16 rest. */
+WQ4_API int32_t wq4_whisper_load_gguf(const char *path, const wq4_whisper_config *cfg, int32_t device,
+                                      wq4_whisper **out);
+WQ4_API int32_t wq4_whisper_load_gguf_memory(const uint8_t *data, size_t nbytes,
+                                             const wq4_whisper_config *cfg, int32_t device,
+                                             wq4_whisper **out);
+WQ4_API int32_t wq4_whisper_destroy(wq4_whisper *m);
+/* Allocates activation / KV-cache workspaces for up to max_batch clips (once, before first use). */
+WQ4_API int32_t wq4_whisper_reserve(wq4_whisper *m, int64_t max_batch);
+WQ4_API int32_t wq4_whisper_info(const wq4_whisper *m, int64_t *d_model, int64_t *ffn, int64_t *vocab,
+                                 int64_t *weight_bytes);
+/* mel_dev [batch, n_mels, 2*n_audio_ctx] f32 -> enc_out_dev [batch, n_audio_ctx, D] f32 (may be NULL:
+ * the encoder output then only stays inside the model for the decoder). */
+WQ4_API int32_t wq4_whisper_encode(wq4_whisper *m, const float *mel_dev, int64_t batch,
+                                   float *enc_out_dev, wq4_stream stream);
+/* Greedy transcription of `batch` clips (see wq4_whisper.cu for the prompt modes).
+ * lang_tokens [batch] (host; < 0 = auto-detect, all clips same mode); tokens_out [batch][224] and
+ * counts_out [batch] (host); detected_lang_out [batch] may be NULL.  Synchronises `stream`. */
+WQ4_API int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t batch,
+                                       const int32_t *lang_tokens, int32_t *tokens_out,
+                                       int32_t *counts_out, int32_t *detected_lang_out,
+                                       wq4_stream stream);
+/* One decoder pass over q_len new tokens per clip after wq4_whisper_encode (test / bench hook);
+ * logits_dev [batch][vocab] of the last position (may be NULL). */
+WQ4_API int32_t wq4_whisper_decoder_pass(wq4_whisper *m, const int32_t *tokens_host, int64_t batch,
+                                         int64_t q_len, int64_t emb_pos0, int64_t kv_pos0,
+                                         int32_t recompute_cross, float *logits_dev, wq4_stream stream);
+/* Stream-ordered greedy decode step on device-resident tokens (CUDA-graph capturable). */
+WQ4_API int32_t wq4_whisper_decode_step_device(wq4_whisper *m, int64_t batch, int64_t position,
+                                               int64_t kv_len, wq4_stream stream);
+
 /* ---- Introspection used by bench.py / tests ------------------------------------------- */
 /* Which kernel family a [rows,K]x[N,K]^T call dispatches to: 0 = GEMV (CUDA cores),
  * 1 = tcgen05 GEMM.  `tile_m` receives the GEMM row tile (0 for GEMV). */
@@ -140,6 +190,12 @@ WQ4_API int32_t wq4_linear_plan(const wq4_tensor *w, int64_t rows, uint32_t flag
 /* Count of kernels this library has launched on the calling thread since the last reset. */
 WQ4_API int64_t wq4_launch_count(void);
 WQ4_API void wq4_launch_count_reset(void);
+/* Per-kernel timing for the roofline leg of bench.py: while enabled, every launch is bracketed by a
+ * CUDA event pair on its stream.  kind: 0 Q4 GEMM (work = flop), 1 dense GEMM (flop), 2 GEMV (bytes),
+ * 3 encoder attention (flop), 4 LayerNorm (bytes), 5 decoder attention (bytes), 6 logits (bytes), 7 other. */
+WQ4_API void wq4_profile_enable(int32_t on);
+WQ4_API void wq4_profile_reset(void);
+WQ4_API int32_t wq4_profile_read(int32_t kind, int64_t *launches, double *ms, double *work);
 /* Sticky device-side error flag set by kernels (pipeline wait timeouts); 0 = clean. */
 WQ4_API int32_t wq4_device_error_flag(int32_t device);
 

@@ -29,6 +29,27 @@ int32_t wq4_cuda_fail(cudaError_t e, const char *what)
 
 void wq4_count_launch(int n) { g_launches += n; }
 
+// ---- per-kernel profiler (bench.py's roofline leg): CUDA event pairs around launches ----------------
+struct ProfRec { int kind; double work; cudaEvent_t e0, e1; };
+static thread_local bool g_prof_on = false;
+static thread_local std::vector<ProfRec> *g_prof = nullptr;
+
+WqProfScope::WqProfScope(int kind, double work, cudaStream_t st) : active(false), stream(st)
+{
+    if (!g_prof_on) return;
+    if (!g_prof) g_prof = new std::vector<ProfRec>();
+    ProfRec r;
+    r.kind = kind; r.work = work;
+    if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return;
+    cudaEventRecord(r.e0, st);
+    g_prof->push_back(r);
+    active = true;
+}
+WqProfScope::~WqProfScope()
+{
+    if (active) cudaEventRecord(g_prof->back().e1, stream);
+}
+
 static std::mutex g_dev_mu;
 static int *g_err_flag[64] = {};
 static int g_sms[64] = {};
@@ -190,6 +211,38 @@ int32_t wq4_device_count(void)
 
 int64_t wq4_launch_count(void) { return g_launches; }
 void wq4_launch_count_reset(void) { g_launches = 0; }
+
+void wq4_profile_enable(int32_t on)
+{
+    g_prof_on = on != 0;
+}
+
+void wq4_profile_reset(void)
+{
+    if (!g_prof) return;
+    for (auto &r : *g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+    g_prof->clear();
+}
+
+int32_t wq4_profile_read(int32_t kind, int64_t *launches, double *ms, double *work)
+{
+    int64_t n = 0;
+    double t = 0.0, w = 0.0;
+    if (g_prof) {
+        for (auto &r : *g_prof) {
+            if (r.kind != kind) continue;
+            float e = 0.0f;
+            cudaError_t st = cudaEventSynchronize(r.e1);
+            if (st == cudaSuccess) st = cudaEventElapsedTime(&e, r.e0, r.e1);
+            if (st != cudaSuccess) return wq4_cuda_fail(st, "wq4_profile_read");
+            n++; t += e; w += r.work;
+        }
+    }
+    if (launches) *launches = n;
+    if (ms) *ms = t;
+    if (work) *work = w;
+    return WQ4_OK;
+}
 
 int32_t wq4_device_error_flag(int32_t device)
 {

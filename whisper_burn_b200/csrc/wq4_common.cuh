@@ -64,6 +64,17 @@ void wq4_count_launch(int n = 1);
 int *wq4_error_flag_ptr(int device);   // device int, sticky, lazily allocated per device
 int wq4_sm_count(int device);
 
+// Profiler scope: when wq4_profile_enable(1) is set, brackets the launches made inside its lifetime
+// with a CUDA event pair on `st` and books `work` (flops or bytes) under `kind`.
+enum { WQ4_PROF_GEMM_Q4 = 0, WQ4_PROF_GEMM_DENSE = 1, WQ4_PROF_GEMV = 2, WQ4_PROF_ATTN_ENC = 3, WQ4_PROF_LAYERNORM = 4,
+       WQ4_PROF_ATTN_DEC = 5, WQ4_PROF_LOGITS = 6, WQ4_PROF_OTHER = 7 };
+struct WqProfScope {
+    bool active;
+    cudaStream_t stream;
+    WqProfScope(int kind, double work, cudaStream_t st);
+    ~WqProfScope();
+};
+
 #define WQ4_CUDA(call)                                            \
     do {                                                          \
         cudaError_t e__ = (call);                                 \

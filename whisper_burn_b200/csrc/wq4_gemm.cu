@@ -607,6 +607,7 @@ int32_t wq4_launch_gemm_q4(const LinearArgs &a, int tile_m)
     p.ob = 0; p.ot = w->n; p.on = 1; p.rb = 0;
     p.flags = a.flags; p.dev_err = wq4_error_flag_ptr(w->device);
     if (!p.dev_err) return WQ4_ERR_CUDA;
+    WqProfScope prof(WQ4_PROF_GEMM_Q4, 2.0 * (double)a.rows * (double)w->n * (double)w->k, a.stream);
     return launch_any<false>(tile_m, bf16, tx, ta, p, w->device, a.stream);
 }
 
@@ -628,5 +629,6 @@ int32_t wq4_launch_gemm_dense(const DenseGemmArgs &a, int tile_m)
     p.ob = a.ob; p.ot = a.ot; p.on = a.on; p.rb = a.rb;
     p.flags = a.flags; p.dev_err = wq4_error_flag_ptr(a.device);
     if (!p.dev_err) return WQ4_ERR_CUDA;
+    WqProfScope prof(WQ4_PROF_GEMM_DENSE, 2.0 * (double)a.x_rows * (double)a.x_batch * (double)a.n * (double)a.x_k, a.stream);
     return launch_any<true>(tile_m, bf16, tx, ta, p, a.device, a.stream);
 }

@@ -232,6 +232,10 @@ int32_t wq4_launch_gemv(const LinearArgs &a)
     while (ks > 1 && (p.kb + ks - 1) / ks < kLanesK) ks >>= 1;
     p.per = (p.kb + ks - 1) / ks;
     int mv = a.rows <= 1 ? 1 : a.rows <= 2 ? 2 : a.rows <= 4 ? 4 : 8;
+    // algorithmic bytes: Q4 weights + x + bias + y
+    const double bytes = (double)w->n * (double)w->k / 32.0 * 18.0 + 4.0 * (double)w->k * (double)a.rows +
+                         (a.bias ? 4.0 * (double)w->n : 0.0) + 4.0 * (double)w->n * (double)a.rows;
+    WqProfScope prof(WQ4_PROF_GEMV, bytes, a.stream);
     switch (mv) {
     case 1: return launch<1>(p, (int)w->np, ks, a.stream);
     case 2: return launch<2>(p, (int)w->np, ks, a.stream);

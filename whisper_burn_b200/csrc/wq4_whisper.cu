@@ -1,0 +1,721 @@
+// wq4_whisper.cu -- host-side C++ of the callers around the Q4 hot path: GGUF reader, model
+// loader, encoder, decoder with in-place KV caches, greedy loop, batched transcribe.
+//
+// Mirrors (file:line under the reference tree):
+//   GgufReader                      src/gguf/reader.rs:98-223
+//   load_whisper_from_gguf & co     src/gguf/loader.rs:26-377 (tensor names, [k,n] -> [n,k], optional biases)
+//   WhisperEncoder::forward         src/model/encoder.rs:37-49,87-115
+//   WhisperDecoder::{forward_prompt,decode_step}   src/model/decoder.rs:77-167,251-348
+//   WhisperModel::transcribe        src/model/whisper.rs:51-138 (prompt modes, EOT suppression, MAX_TOKENS)
+//   transcribe (batching is new)    src/transcribe.rs:34-107
+// Differences by design: q/k/v (and cross k/v) projections are fused into one Q4 weight at load; the
+// KV caches are preallocated f16 buffers written in place (no Tensor::cat realloc, attention.rs:106-113);
+// argmax runs on the device; utterances are batched (M = 1500*B in the encoder, M = B in the decoder).
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "wq4_common.cuh"
+#include "wq4_model.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------ GGUF reader
+struct GgufTensor {
+    std::vector<uint64_t> dims;   // as stored (reversed w.r.t. row-major shape)
+    uint32_t dtype;               // 0 F32, 1 F16, 2 Q4_0 (reader.rs:27-35)
+    uint64_t offset;
+    uint64_t num_elements() const { uint64_t n = 1; for (auto d : dims) n *= d; return n; }
+    uint64_t byte_size() const    // reader.rs:38-48
+    {
+        uint64_t n = num_elements();
+        return dtype == 0 ? n * 4 : dtype == 1 ? n * 2 : n / 32 * 18;
+    }
+};
+
+struct Gguf {
+    const uint8_t *data = nullptr;
+    size_t size = 0;
+    uint32_t version = 0;
+    uint64_t tensor_count = 0;
+    uint64_t data_offset = 0;
+    std::map<std::string, GgufTensor> tensors;
+    std::string err;
+
+    bool rd(size_t &pos, void *dst, size_t n)
+    {
+        if (pos + n > size) { err = "unexpected end of GGUF data"; return false; }
+        memcpy(dst, data + pos, n);
+        pos += n;
+        return true;
+    }
+    bool rd_str(size_t &pos, std::string &s)
+    {
+        uint64_t n;
+        if (!rd(pos, &n, 8)) return false;
+        if (pos + n > size) { err = "unexpected end of GGUF string"; return false; }
+        s.assign(reinterpret_cast<const char *>(data + pos), (size_t)n);
+        pos += (size_t)n;
+        return true;
+    }
+    bool skip_value(size_t &pos, uint32_t t)   // reader.rs:237-285
+    {
+        static const int sz[13] = {1, 1, 2, 2, 4, 4, 4, 1, -1, -2, 8, 8, 8};
+        if (t > 12) { err = "Unknown GGUF metadata value type"; return false; }
+        if (sz[t] > 0) { if (pos + sz[t] > size) { err = "truncated metadata"; return false; } pos += sz[t]; return true; }
+        if (t == 8) { std::string s; return rd_str(pos, s); }
+        uint32_t et; uint64_t cnt;
+        if (!rd(pos, &et, 4) || !rd(pos, &cnt, 8)) return false;
+        for (uint64_t i = 0; i < cnt; i++) if (!skip_value(pos, et)) return false;
+        return true;
+    }
+    bool parse(const uint8_t *d, size_t n)     // reader.rs:105-188
+    {
+        data = d; size = n;
+        size_t pos = 0;
+        uint32_t magic;
+        if (!rd(pos, &magic, 4)) return false;
+        if (magic != 0x46554747u) { err = "Invalid GGUF magic"; return false; }
+        if (!rd(pos, &version, 4)) return false;
+        if (version != 2 && version != 3) { err = "Unsupported GGUF version (expected 2 or 3)"; return false; }
+        uint64_t kv;
+        if (!rd(pos, &tensor_count, 8) || !rd(pos, &kv, 8)) return false;
+        for (uint64_t i = 0; i < kv; i++) {
+            std::string key; uint32_t vt;
+            if (!rd_str(pos, key) || !rd(pos, &vt, 4) || !skip_value(pos, vt)) return false;
+        }
+        for (uint64_t i = 0; i < tensor_count; i++) {
+            std::string name; uint32_t nd;
+            GgufTensor t;
+            if (!rd_str(pos, name) || !rd(pos, &nd, 4)) return false;
+            if (nd > 8) { err = "tensor rank too large"; return false; }
+            t.dims.resize(nd);
+            for (uint32_t j = 0; j < nd; j++) if (!rd(pos, &t.dims[j], 8)) return false;
+            if (!rd(pos, &t.dtype, 4) || !rd(pos, &t.offset, 8)) return false;
+            if (t.dtype > 2) { err = "Unsupported GGML dtype code"; return false; }
+            tensors[name] = t;
+        }
+        data_offset = (pos + 31) / 32 * 32;    // reader.rs:178-179
+        return true;
+    }
+    const GgufTensor *find(const std::string &name) const
+    {
+        auto it = tensors.find(name);
+        return it == tensors.end() ? nullptr : &it->second;
+    }
+    const uint8_t *tensor_data(const GgufTensor &t) const
+    {
+        uint64_t a = data_offset + t.offset;
+        if (a + t.byte_size() > size) return nullptr;
+        return data + a;
+    }
+};
+
+static float f16_bits_to_f32(uint16_t h)
+{
+    __half hv = __ushort_as_half(h);
+    return __half2float(hv);
+}
+
+// ------------------------------------------------------------------------------------------ model
+struct Lin { wq4_tensor *w = nullptr; float *bias = nullptr; };
+struct LNp { float *w = nullptr; float *b = nullptr; };
+struct EncLayer { LNp attn_ln; Lin qkv, out; LNp mlp_ln; Lin fc1, fc2; };
+struct DecLayer { LNp attn_ln; Lin qkv, out; LNp cross_ln; Lin cq, ckv, cout; LNp mlp_ln; Lin fc1, fc2; };
+
+}  // namespace
+
+struct wq4_whisper {
+    wq4_whisper_config cfg;
+    int device = 0;
+    int64_t D = 0, F = 0, V = 0, T_mel = 3000, T_enc = 1500;
+    wq4_conv1d *conv1 = nullptr, *conv2 = nullptr;
+    float *enc_pos = nullptr;        // [n_audio_ctx, D]
+    std::vector<EncLayer> enc;
+    LNp ln_post;
+    float *tok_emb = nullptr;        // [V, D] f32 (decoder.rs:171, logits matmul :292,343)
+    float *dec_pos = nullptr;        // [n_text_ctx, D]
+    std::vector<DecLayer> dec;
+    LNp ln;
+    std::vector<void *> owned;       // device allocations freed at destroy
+    size_t weight_bytes = 0;
+    // workspaces (reserved for max_batch)
+    int64_t max_batch = 0;
+    __half *mel_t16 = nullptr, *h1_16 = nullptr, *xn16 = nullptr, *qkv16 = nullptr, *att16 = nullptr, *ffn16 = nullptr,
+           *enc16 = nullptr;
+    float *x = nullptr, *enc32 = nullptr;
+    int64_t Cp1 = 0, Tp1 = 0, Tp2 = 0;
+    // decoder state
+    __half *cross_kv = nullptr;      // [L][B*T_enc][2D]
+    __half *self_k = nullptr, *self_v = nullptr;   // [L][B][n_text_ctx][D]
+    float *dx = nullptr, *dxn = nullptr, *dqkv = nullptr, *datt = nullptr, *dq = nullptr, *dh = nullptr, *logits = nullptr;
+    int *d_tokens = nullptr, *d_next = nullptr, *d_sup_eot = nullptr, *d_sup_none = nullptr;
+    int *h_next = nullptr;           // pinned
+    void *lin_ws = nullptr;
+    size_t lin_ws_bytes = 0;
+    int64_t max_q = 8;               // rows per batch item in one decoder call (prompt <= 4 tokens)
+};
+
+namespace {
+
+#define CHK(st_)                          \
+    do {                                  \
+        int32_t s__ = (st_);              \
+        if (s__ != WQ4_OK) return s__;    \
+    } while (0)
+
+template <typename T>
+int32_t dev_alloc(wq4_whisper *m, T **p, size_t count)
+{
+    void *q = nullptr;
+    WQ4_CUDA(cudaMalloc(&q, count * sizeof(T) > 0 ? count * sizeof(T) : 16));
+    m->owned.push_back(q);
+    *p = reinterpret_cast<T *>(q);
+    return WQ4_OK;
+}
+
+int32_t upload_f32(wq4_whisper *m, const Gguf &g, const std::string &name, float **out, uint64_t expect_elems,
+                   std::vector<float> *host_copy = nullptr)
+{
+    const GgufTensor *t = g.find(name);
+    if (!t) { wq4_set_error("Tensor '%s' not found", name.c_str()); return WQ4_ERR_INVALID; }
+    const uint8_t *raw = g.tensor_data(*t);
+    if (!raw) { wq4_set_error("Tensor '%s' data out of range", name.c_str()); return WQ4_ERR_BYTES; }
+    uint64_t n = t->num_elements();
+    if (expect_elems && n != expect_elems) {
+        wq4_set_error("Tensor '%s' has %llu elements, expected %llu", name.c_str(), (unsigned long long)n, (unsigned long long)expect_elems);
+        return WQ4_ERR_SHAPE;
+    }
+    std::vector<float> host(n);
+    if (t->dtype == 0) memcpy(host.data(), raw, n * 4);
+    else if (t->dtype == 1) { const uint16_t *h = reinterpret_cast<const uint16_t *>(raw); for (uint64_t i = 0; i < n; i++) host[i] = f16_bits_to_f32(h[i]); }
+    else { wq4_set_error("Expected F32/F16 for '%s'", name.c_str()); return WQ4_ERR_INVALID; }   // loader.rs:75,108
+    CHK(dev_alloc(m, out, n));
+    WQ4_CUDA(cudaMemcpy(*out, host.data(), n * 4, cudaMemcpyHostToDevice));
+    m->weight_bytes += n * 4;
+    if (host_copy) host_copy->swap(host);
+    return WQ4_OK;
+}
+
+// load_q4_linear (loader.rs:112-148) for one or several projections fused along N.
+int32_t load_q4_fused(wq4_whisper *m, const Gguf &g, const std::vector<std::string> &prefixes, Lin *out)
+{
+    std::vector<uint8_t> bytes;
+    std::vector<float> bias;
+    bool any_bias = false;
+    int64_t k = -1, n_total = 0;
+    for (const auto &pfx : prefixes) {
+        const std::string wn = pfx + ".weight", bn = pfx + ".bias";
+        const GgufTensor *t = g.find(wn);
+        if (!t) { wq4_set_error("Tensor '%s' not found", wn.c_str()); return WQ4_ERR_INVALID; }
+        if (t->dtype != 2) { wq4_set_error("Expected Q4_0 for weight '%s'. Use the conversion script.", wn.c_str()); return WQ4_ERR_INVALID; }  // loader.rs:132-134
+        if (t->dims.size() != 2) { wq4_set_error("Weight '%s' is not 2-D", wn.c_str()); return WQ4_ERR_SHAPE; }
+        int64_t kk = (int64_t)t->dims[0], nn = (int64_t)t->dims[1];   // GGUF [k, n] -> [n, k] (loader.rs:126-131)
+        if (k >= 0 && kk != k) { wq4_set_error("fused projections disagree on K"); return WQ4_ERR_SHAPE; }
+        k = kk;
+        const uint8_t *raw = g.tensor_data(*t);
+        if (!raw) { wq4_set_error("Tensor '%s' data out of range", wn.c_str()); return WQ4_ERR_BYTES; }
+        bytes.insert(bytes.end(), raw, raw + t->byte_size());
+        bias.resize(n_total + nn, 0.0f);
+        if (const GgufTensor *bt = g.find(bn)) {               // bias optional (loader.rs:137-145)
+            const uint8_t *braw = g.tensor_data(*bt);
+            if (!braw || bt->num_elements() != (uint64_t)nn) { wq4_set_error("Bias '%s' malformed", bn.c_str()); return WQ4_ERR_SHAPE; }
+            if (bt->dtype == 0) memcpy(bias.data() + n_total, braw, nn * 4);
+            else if (bt->dtype == 1) { const uint16_t *h = reinterpret_cast<const uint16_t *>(braw); for (int64_t i = 0; i < nn; i++) bias[n_total + i] = f16_bits_to_f32(h[i]); }
+            else { wq4_set_error("Expected F32/F16 for '%s'", bn.c_str()); return WQ4_ERR_INVALID; }
+            any_bias = true;
+        }
+        n_total += nn;
+    }
+    CHK(wq4_tensor_create(bytes.data(), bytes.size(), n_total, k, m->device, nullptr, &out->w));
+    m->weight_bytes += wq4_tensor_device_bytes(out->w);
+    out->bias = nullptr;
+    if (any_bias) {
+        CHK(dev_alloc(m, &out->bias, (size_t)n_total));
+        WQ4_CUDA(cudaMemcpy(out->bias, bias.data(), n_total * 4, cudaMemcpyHostToDevice));
+    }
+    return WQ4_OK;
+}
+
+int32_t load_ln(wq4_whisper *m, const Gguf &g, const std::string &pfx, LNp *ln, uint64_t D)   // loader.rs:150-158
+{
+    CHK(upload_f32(m, g, pfx + ".weight", &ln->w, D));
+    return upload_f32(m, g, pfx + ".bias", &ln->b, D);
+}
+
+int32_t load_conv(wq4_whisper *m, const Gguf &g, const std::string &pfx, wq4_conv1d **out, int64_t *c_out, int64_t *c_in)
+{
+    const GgufTensor *t = g.find(pfx + ".weight");
+    if (!t || t->dims.size() != 3) { wq4_set_error("Tensor '%s.weight' not found or not 3-D", pfx.c_str()); return WQ4_ERR_INVALID; }
+    int64_t ks = (int64_t)t->dims[0], ci = (int64_t)t->dims[1], co = (int64_t)t->dims[2];   // loader.rs:256-258
+    std::vector<float> w, b;
+    float *tmp = nullptr;
+    CHK(upload_f32(m, g, pfx + ".weight", &tmp, (uint64_t)(ks * ci * co), &w));   // row-major [out, in, k] (loader.rs:273-276)
+    CHK(upload_f32(m, g, pfx + ".bias", &tmp, (uint64_t)co, &b));
+    CHK(wq4_conv1d_create(w.data(), b.data(), co, ci, ks, m->device, nullptr, out));
+    *c_out = co; *c_in = ci;
+    return WQ4_OK;
+}
+
+int32_t load_model(wq4_whisper *m, const Gguf &g)
+{
+    const wq4_whisper_config &c = m->cfg;
+    int64_t co, ci;
+    CHK(load_conv(m, g, "encoder.conv1", &m->conv1, &co, &ci));           // loader.rs:291-296
+    if (ci != c.n_mels) { wq4_set_error("conv1 expects %lld mel bins, config says %d", (long long)ci, c.n_mels); return WQ4_ERR_SHAPE; }
+    m->D = co;
+    CHK(load_conv(m, g, "encoder.conv2", &m->conv2, &co, &ci));           // loader.rs:297-302
+    if (co != m->D || ci != m->D) { wq4_set_error("conv2 must be D x D"); return WQ4_ERR_SHAPE; }
+    if (m->D != c.n_audio_state || m->D != c.n_text_state) { wq4_set_error("state size mismatch: tensors %lld, config %d/%d", (long long)m->D, c.n_audio_state, c.n_text_state); return WQ4_ERR_SHAPE; }
+    if (m->D != (int64_t)c.n_audio_head * 64 || m->D != (int64_t)c.n_text_head * 64) { wq4_set_error("head_dim must be 64 (attention.rs:30)"); return WQ4_ERR_SHAPE; }
+    const uint64_t D = (uint64_t)m->D;
+    CHK(upload_f32(m, g, "encoder.positional_embedding", &m->enc_pos, 0));   // loader.rs:304
+    {
+        const GgufTensor *t = g.find("encoder.positional_embedding");
+        if (t->dims.size() != 2 || t->dims[0] != D || (int64_t)t->dims[1] < m->T_enc) { wq4_set_error("encoder.positional_embedding must be [>=1500, D]"); return WQ4_ERR_SHAPE; }
+    }
+    m->enc.resize(c.n_audio_layer);
+    for (int i = 0; i < c.n_audio_layer; i++) {                            // loader.rs:306-323
+        const std::string p = "encoder.blocks." + std::to_string(i);
+        EncLayer &L = m->enc[i];
+        CHK(load_ln(m, g, p + ".attn_ln", &L.attn_ln, D));
+        CHK(load_q4_fused(m, g, {p + ".attn.query", p + ".attn.key", p + ".attn.value"}, &L.qkv));   // loader.rs:160-191
+        CHK(load_q4_fused(m, g, {p + ".attn.out"}, &L.out));
+        CHK(load_ln(m, g, p + ".mlp_ln", &L.mlp_ln, D));
+        CHK(load_q4_fused(m, g, {p + ".mlp.0"}, &L.fc1));                  // loader.rs:226-244
+        CHK(load_q4_fused(m, g, {p + ".mlp.2"}, &L.fc2));
+        int64_t n, k;
+        wq4_tensor_shape(L.fc1.w, &n, &k);
+        m->F = n;
+    }
+    CHK(load_ln(m, g, "encoder.ln_post", &m->ln_post, D));                 // loader.rs:325
+    CHK(upload_f32(m, g, "decoder.token_embedding.weight", &m->tok_emb, 0));   // loader.rs:338-339
+    {
+        const GgufTensor *t = g.find("decoder.token_embedding.weight");
+        if (t->dims.size() != 2 || t->dims[0] != D) { wq4_set_error("token embedding must be [V, D]"); return WQ4_ERR_SHAPE; }
+        m->V = (int64_t)t->dims[1];   // vocabulary size comes from the tensor (config.n_vocab is never read by the reference)
+    }
+    CHK(upload_f32(m, g, "decoder.positional_embedding", &m->dec_pos, 0));     // loader.rs:340-341
+    {
+        const GgufTensor *t = g.find("decoder.positional_embedding");
+        if (t->dims.size() != 2 || t->dims[0] != D || (int64_t)t->dims[1] < c.n_text_ctx) { wq4_set_error("decoder.positional_embedding must be [>=n_text_ctx, D]"); return WQ4_ERR_SHAPE; }
+    }
+    m->dec.resize(c.n_text_layer);
+    for (int i = 0; i < c.n_text_layer; i++) {                             // loader.rs:343-367
+        const std::string p = "decoder.blocks." + std::to_string(i);
+        DecLayer &L = m->dec[i];
+        CHK(load_ln(m, g, p + ".attn_ln", &L.attn_ln, D));
+        CHK(load_q4_fused(m, g, {p + ".attn.query", p + ".attn.key", p + ".attn.value"}, &L.qkv));
+        CHK(load_q4_fused(m, g, {p + ".attn.out"}, &L.out));
+        CHK(load_ln(m, g, p + ".cross_attn_ln", &L.cross_ln, D));
+        CHK(load_q4_fused(m, g, {p + ".cross_attn.query"}, &L.cq));        // loader.rs:193-224 (key has no bias :208)
+        CHK(load_q4_fused(m, g, {p + ".cross_attn.key", p + ".cross_attn.value"}, &L.ckv));
+        CHK(load_q4_fused(m, g, {p + ".cross_attn.out"}, &L.cout));
+        CHK(load_ln(m, g, p + ".mlp_ln", &L.mlp_ln, D));
+        CHK(load_q4_fused(m, g, {p + ".mlp.0"}, &L.fc1));
+        CHK(load_q4_fused(m, g, {p + ".mlp.2"}, &L.fc2));
+    }
+    return load_ln(m, g, "decoder.ln", &m->ln, D);                         // loader.rs:369
+}
+
+int32_t reserve(wq4_whisper *m, int64_t B)
+{
+    if (B <= m->max_batch) return WQ4_OK;
+    if (m->max_batch != 0) { wq4_set_error("wq4_whisper_reserve: batch can only be reserved once (have %lld, asked %lld)", (long long)m->max_batch, (long long)B); return WQ4_ERR_INVALID; }
+    const int64_t D = m->D, F = m->F, T = m->T_enc, Ld = (int64_t)m->dec.size(), ctx = m->cfg.n_text_ctx;
+    m->Cp1 = (m->cfg.n_mels + 7) / 8 * 8;
+    m->Tp1 = m->T_mel + 2;
+    m->Tp2 = m->T_mel + 2;   // even, as the stride-2 view requires
+    const int64_t M = B * T;
+    CHK(dev_alloc(m, &m->mel_t16, (size_t)(B * m->Tp1 + 4) * m->Cp1));
+    CHK(dev_alloc(m, &m->h1_16, (size_t)(B * m->Tp2 + 4) * D));
+    WQ4_CUDA(cudaMemset(m->h1_16, 0, (size_t)(B * m->Tp2 + 4) * D * 2));   // pad rows stay zero forever
+    CHK(dev_alloc(m, &m->x, (size_t)M * D));
+    CHK(dev_alloc(m, &m->xn16, (size_t)M * D));
+    CHK(dev_alloc(m, &m->qkv16, (size_t)M * 3 * D));
+    CHK(dev_alloc(m, &m->att16, (size_t)M * D));
+    CHK(dev_alloc(m, &m->ffn16, (size_t)M * F));
+    CHK(dev_alloc(m, &m->enc16, (size_t)M * D));
+    CHK(dev_alloc(m, &m->enc32, (size_t)M * D));
+    CHK(dev_alloc(m, &m->cross_kv, (size_t)Ld * M * 2 * D));
+    CHK(dev_alloc(m, &m->self_k, (size_t)Ld * B * ctx * D));
+    CHK(dev_alloc(m, &m->self_v, (size_t)Ld * B * ctx * D));
+    const int64_t R = B * m->max_q;
+    CHK(dev_alloc(m, &m->dx, (size_t)R * D));
+    CHK(dev_alloc(m, &m->dxn, (size_t)R * D));
+    CHK(dev_alloc(m, &m->dqkv, (size_t)R * 3 * D));
+    CHK(dev_alloc(m, &m->datt, (size_t)R * D));
+    CHK(dev_alloc(m, &m->dq, (size_t)R * D));
+    CHK(dev_alloc(m, &m->dh, (size_t)R * F));
+    CHK(dev_alloc(m, &m->logits, (size_t)B * m->V));
+    CHK(dev_alloc(m, &m->d_tokens, (size_t)R));
+    CHK(dev_alloc(m, &m->d_next, (size_t)B));
+    CHK(dev_alloc(m, &m->d_sup_eot, (size_t)B));
+    CHK(dev_alloc(m, &m->d_sup_none, (size_t)B));
+    std::vector<int> e((size_t)B, 50257), n((size_t)B, -1);
+    WQ4_CUDA(cudaMemcpy(m->d_sup_eot, e.data(), B * 4, cudaMemcpyHostToDevice));
+    WQ4_CUDA(cudaMemcpy(m->d_sup_none, n.data(), B * 4, cudaMemcpyHostToDevice));
+    WQ4_CUDA(cudaMallocHost(&m->h_next, (size_t)B * 4));
+    m->lin_ws_bytes = (size_t)R * (size_t)F * 2 + 4096;   // f32 -> f16 copy of the widest decoder activation
+    CHK(dev_alloc(m, reinterpret_cast<uint8_t **>(&m->lin_ws), m->lin_ws_bytes));
+    m->max_batch = B;
+    return WQ4_OK;
+}
+
+int32_t lin16(const Lin &l, const void *x16, float *y32, void *y16, const float *res, int64_t rows, uint32_t flags, cudaStream_t st)
+{
+    return wq4_linear_forward_ex(l.w, l.bias, nullptr, x16, y32, y16, res, rows, flags, nullptr, 0, st);
+}
+int32_t lin32(wq4_whisper *m, const Lin &l, const float *x, float *y, const float *res, int64_t rows, uint32_t flags, cudaStream_t st)
+{
+    return wq4_linear_forward_ex(l.w, l.bias, x, nullptr, y, nullptr, res, rows, flags, m->lin_ws, m->lin_ws_bytes, st);
+}
+
+// WhisperEncoder::forward (encoder.rs:87-115) for B clips; mel_dev [B, n_mels, 3000] f32.
+int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
+{
+    const int64_t D = m->D, T = m->T_enc, M = B * T;
+    const wq4_whisper_config &c = m->cfg;
+    // mel -> time-major f16 with one zero row before/after each clip (padding 1, layers.rs:83-90)
+    CHK(wq4m_mel_transpose(mel_dev, m->mel_t16, B, c.n_mels, m->T_mel, m->Cp1, m->Tp1, 1, st));
+    // conv1 (k=3, p=1, s=1) + GELU -> h1 [B][3002][D] f16, rows 1..3000 (encoder.rs:89-90)
+    DenseGemmArgs a = {};
+    a.w16 = m->conv1->w16; a.x16 = m->mel_t16; a.bias = m->conv1->bias; a.residual = nullptr;
+    a.y_f32 = nullptr; a.y_f16 = m->h1_16 + D;
+    a.n = D; a.n_pad = m->conv1->rows_pad; a.kdim_pad = m->conv1->kdim_pad;
+    a.x_k = 3 * m->Cp1; a.x_rows = m->T_mel; a.x_batch = B; a.x_row_stride = m->Cp1; a.x_batch_stride = m->Tp1 * m->Cp1;
+    a.ob = m->Tp2 * D; a.ot = D; a.on = 1; a.rb = 0;
+    a.flags = WQ4_EPI_GELU; a.device = m->device; a.stream = st;
+    CHK(wq4_launch_gemm_dense(a, wq4_pick_tile_m(m->T_mel, a.n_pad / WQ4_PANEL_ROWS * B)));
+    // conv2 (k=3, p=1, s=2) + GELU + positional embedding -> x [B*1500][D] f32 (encoder.rs:93-106)
+    DenseGemmArgs b2 = {};
+    b2.w16 = m->conv2->w16; b2.x16 = m->h1_16; b2.bias = m->conv2->bias; b2.residual = m->enc_pos;
+    b2.y_f32 = m->x; b2.y_f16 = nullptr;
+    b2.n = D; b2.n_pad = m->conv2->rows_pad; b2.kdim_pad = m->conv2->kdim_pad;
+    b2.x_k = 3 * D; b2.x_rows = T; b2.x_batch = B; b2.x_row_stride = 2 * D; b2.x_batch_stride = m->Tp2 * D;
+    b2.ob = T * D; b2.ot = D; b2.on = 1; b2.rb = 0;
+    b2.flags = WQ4_EPI_GELU; b2.device = m->device; b2.stream = st;
+    CHK(wq4_launch_gemm_dense(b2, wq4_pick_tile_m(T, b2.n_pad / WQ4_PANEL_ROWS * B)));
+    for (auto &L : m->enc) {                                               // EncoderBlock::forward, encoder.rs:37-49
+        CHK(wq4m_layernorm(m->x, L.attn_ln.w, L.attn_ln.b, nullptr, m->xn16, M, D, st));
+        CHK(lin16(L.qkv, m->xn16, nullptr, m->qkv16, nullptr, M, 0, st));
+        CHK(wq4m_enc_attention(m->qkv16, m->att16, B, T, D, c.n_audio_head, st));
+        CHK(lin16(L.out, m->att16, m->x, nullptr, m->x, M, 0, st));        // residual + attn
+        CHK(wq4m_layernorm(m->x, L.mlp_ln.w, L.mlp_ln.b, nullptr, m->xn16, M, D, st));
+        CHK(lin16(L.fc1, m->xn16, nullptr, m->ffn16, nullptr, M, WQ4_EPI_GELU, st));
+        CHK(lin16(L.fc2, m->ffn16, m->x, nullptr, m->x, M, 0, st));        // residual + ffn
+    }
+    return wq4m_layernorm(m->x, m->ln_post.w, m->ln_post.b, m->enc32, m->enc16, M, D, st);   // encoder.rs:114
+}
+
+// Cross-attention K/V for every decoder layer from the encoder output (attention.rs:185-186):
+// one fused [2D, D] GEMM at M = 1500*B per layer, stored f16.
+int32_t cross_kv(wq4_whisper *m, int64_t B, cudaStream_t st)
+{
+    const int64_t D = m->D, M = B * m->T_enc;
+    for (size_t l = 0; l < m->dec.size(); l++)
+        CHK(lin16(m->dec[l].ckv, m->enc16, nullptr, m->cross_kv + l * (size_t)M * 2 * D, nullptr, M, 0, st));
+    return WQ4_OK;
+}
+
+// One decoder pass over q_len new positions per clip (forward_prompt / decode_step, decoder.rs:251-348).
+//   emb_pos0 : first positional-embedding row;  kv_pos0 : self-attention cache rows already valid
+//   (the prompt pass overwrites from 0, decoder.rs:149-151).  Leaves logits of the LAST position.
+int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, cudaStream_t st)
+{
+    const int64_t D = m->D, F = m->F, R = B * q_len, ctx = m->cfg.n_text_ctx, H = m->cfg.n_text_head;
+    const int64_t M = B * m->T_enc;
+    if (q_len > m->max_q || kv_pos0 + q_len > ctx || emb_pos0 + q_len > ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
+    CHK(wq4m_embed(m->d_tokens, m->tok_emb, m->dec_pos, m->dx, B, q_len, D, emb_pos0, st));
+    for (size_t l = 0; l < m->dec.size(); l++) {
+        DecLayer &L = m->dec[l];
+        __half *sk = m->self_k + l * (size_t)B * ctx * D, *sv = m->self_v + l * (size_t)B * ctx * D;
+        const __half *ck = m->cross_kv + l * (size_t)M * 2 * D;
+        // self-attention with cache (decoder.rs:84-92 / 147-152)
+        CHK(wq4m_layernorm(m->dx, L.attn_ln.w, L.attn_ln.b, m->dxn, nullptr, R, D, st));
+        CHK(lin32(m, L.qkv, m->dxn, m->dqkv, nullptr, R, 0, st));
+        CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
+        CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, q_len, kv_pos0 + q_len,
+                               q_len > 1 ? (int)kv_pos0 : -1, st));
+        CHK(lin32(m, L.out, m->datt, m->dx, m->dx, R, 0, st));
+        // cross-attention over the cached encoder K/V (decoder.rs:95-104)
+        CHK(wq4m_layernorm(m->dx, L.cross_ln.w, L.cross_ln.b, m->dxn, nullptr, R, D, st));
+        CHK(lin32(m, L.cq, m->dxn, m->dq, nullptr, R, 0, st));
+        CHK(wq4m_dec_attention(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, q_len, m->T_enc, -1, st));
+        CHK(lin32(m, L.cout, m->datt, m->dx, m->dx, R, 0, st));
+        // FFN (decoder.rs:107-110)
+        CHK(wq4m_layernorm(m->dx, L.mlp_ln.w, L.mlp_ln.b, m->dxn, nullptr, R, D, st));
+        CHK(lin32(m, L.fc1, m->dxn, m->dh, nullptr, R, WQ4_EPI_GELU, st));
+        CHK(lin32(m, L.fc2, m->dh, m->dx, m->dx, R, 0, st));
+    }
+    // final LN on the last position of every clip, then logits = x . token_embedding^T (decoder.rs:286-292)
+    if (q_len == 1) {
+        CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, B, D, st));
+    } else {
+        CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, R, D, st));
+        // gather last rows: dxn[b*q_len + q_len-1] -> dq[b]
+        WQ4_CUDA(cudaMemcpy2DAsync(m->dq, D * 4, m->dxn + (q_len - 1) * D, q_len * D * 4, D * 4, B, cudaMemcpyDeviceToDevice, st));
+    }
+    const float *last = q_len == 1 ? m->dxn : m->dq;
+    (void)F;
+    return wq4m_logits(last, m->tok_emb, m->logits, B, D, m->V, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t wq4_whisper_config_preset(const char *name, wq4_whisper_config *cfg)
+{
+    if (!name || !cfg) { wq4_set_error("wq4_whisper_config_preset: null argument"); return WQ4_ERR_INVALID; }
+    wq4_whisper_config c = {};
+    c.n_audio_ctx = 1500; c.n_text_ctx = 448; c.n_vocab = 51865;
+    if (!strcmp(name, "large_v3")) {          // config.rs:32-46
+        c.n_mels = 128; c.n_audio_state = 1280; c.n_audio_head = 20; c.n_audio_layer = 32;
+        c.n_text_state = 1280; c.n_text_head = 20; c.n_text_layer = 32; c.n_lang = 100;
+    } else if (!strcmp(name, "medium")) {     // config.rs:49-63
+        c.n_mels = 80; c.n_audio_state = 1024; c.n_audio_head = 16; c.n_audio_layer = 24;
+        c.n_text_state = 1024; c.n_text_head = 16; c.n_text_layer = 24; c.n_lang = 99;
+    } else {
+        wq4_set_error("unknown preset '%s' (large_v3 | medium)", name);
+        return WQ4_ERR_INVALID;
+    }
+    *cfg = c;
+    return WQ4_OK;
+}
+
+int32_t wq4_whisper_load_gguf_memory(const uint8_t *data, size_t nbytes, const wq4_whisper_config *cfg, int32_t device,
+                                     wq4_whisper **out)
+{
+    if (!data || !cfg || !out) { wq4_set_error("wq4_whisper_load_gguf_memory: null argument"); return WQ4_ERR_INVALID; }
+    *out = nullptr;
+    Gguf g;
+    if (!g.parse(data, nbytes)) { wq4_set_error("Failed to parse GGUF: %s", g.err.c_str()); return WQ4_ERR_INVALID; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        cudaGetLastError();
+        wq4_set_error("wq4_whisper_load: CUDA device %d not available (%d visible); there is no CPU fallback", device, ndev);
+        return WQ4_ERR_CUDA;
+    }
+    DeviceGuard guard(device);
+    wq4_whisper *m = new wq4_whisper();
+    m->cfg = *cfg;
+    m->device = device;
+    m->T_enc = cfg->n_audio_ctx;
+    m->T_mel = 2 * (int64_t)cfg->n_audio_ctx;
+    int32_t st = load_model(m, g);
+    if (st != WQ4_OK) { wq4_whisper_destroy(m); return st; }
+    *out = m;
+    return WQ4_OK;
+}
+
+int32_t wq4_whisper_load_gguf(const char *path, const wq4_whisper_config *cfg, int32_t device, wq4_whisper **out)
+{
+    if (!path || !cfg || !out) { wq4_set_error("wq4_whisper_load_gguf: null argument"); return WQ4_ERR_INVALID; }
+    FILE *f = fopen(path, "rb");
+    if (!f) { wq4_set_error("Failed to open GGUF file: %s", path); return WQ4_ERR_INVALID; }   // loader.rs:31-32
+    fseek(f, 0, SEEK_END);
+    long n = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    std::vector<uint8_t> buf((size_t)n);
+    size_t got = fread(buf.data(), 1, (size_t)n, f);
+    fclose(f);
+    if (got != (size_t)n) { wq4_set_error("short read on %s", path); return WQ4_ERR_INVALID; }
+    return wq4_whisper_load_gguf_memory(buf.data(), buf.size(), cfg, device, out);
+}
+
+int32_t wq4_whisper_destroy(wq4_whisper *m)
+{
+    if (!m) return WQ4_OK;
+    DeviceGuard g(m->device);
+    for (auto &L : m->enc) { wq4_tensor_destroy(L.qkv.w); wq4_tensor_destroy(L.out.w); wq4_tensor_destroy(L.fc1.w); wq4_tensor_destroy(L.fc2.w); }
+    for (auto &L : m->dec) {
+        wq4_tensor_destroy(L.qkv.w); wq4_tensor_destroy(L.out.w); wq4_tensor_destroy(L.cq.w); wq4_tensor_destroy(L.ckv.w);
+        wq4_tensor_destroy(L.cout.w); wq4_tensor_destroy(L.fc1.w); wq4_tensor_destroy(L.fc2.w);
+    }
+    wq4_conv1d_destroy(m->conv1);
+    wq4_conv1d_destroy(m->conv2);
+    for (void *p : m->owned) cudaFree(p);
+    if (m->h_next) cudaFreeHost(m->h_next);
+    delete m;
+    return WQ4_OK;
+}
+
+int32_t wq4_whisper_reserve(wq4_whisper *m, int64_t max_batch)
+{
+    if (!m || max_batch <= 0) { wq4_set_error("wq4_whisper_reserve: invalid argument"); return WQ4_ERR_INVALID; }
+    DeviceGuard g(m->device);
+    return reserve(m, max_batch);
+}
+
+int32_t wq4_whisper_info(const wq4_whisper *m, int64_t *d_model, int64_t *ffn, int64_t *vocab, int64_t *weight_bytes)
+{
+    if (!m) { wq4_set_error("wq4_whisper_info: null model"); return WQ4_ERR_INVALID; }
+    if (d_model) *d_model = m->D;
+    if (ffn) *ffn = m->F;
+    if (vocab) *vocab = m->V;
+    if (weight_bytes) *weight_bytes = (int64_t)m->weight_bytes;
+    return WQ4_OK;
+}
+
+int32_t wq4_whisper_encode(wq4_whisper *m, const float *mel_dev, int64_t batch, float *enc_out_dev, wq4_stream stream)
+{
+    if (!m || !mel_dev || batch <= 0) { wq4_set_error("wq4_whisper_encode: invalid argument"); return WQ4_ERR_INVALID; }
+    DeviceGuard g(m->device);
+    CHK(reserve(m, batch));
+    if (batch > m->max_batch) { wq4_set_error("wq4_whisper_encode: batch %lld exceeds the reserved %lld", (long long)batch, (long long)m->max_batch); return WQ4_ERR_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    CHK(encode(m, mel_dev, batch, st));
+    if (enc_out_dev)
+        WQ4_CUDA(cudaMemcpyAsync(enc_out_dev, m->enc32, (size_t)batch * m->T_enc * m->D * 4, cudaMemcpyDeviceToDevice, st));
+    return WQ4_OK;
+}
+
+// WhisperModel::transcribe (whisper.rs:51-128) for a batch of clips that share the prompt mode.
+//   lang_tokens[b] >= 0 : explicit language -> prompt [SOT, lang, TRANSCRIBE, NO_TIMESTAMPS] (whisper.rs:67-71)
+//   lang_tokens[b] <  0 : auto-detect       -> decode_step(SOT, 0), argmax over the language range, then
+//                         prompt [lang, TRANSCRIBE, NO_TIMESTAMPS] at positions 0..3 with the self-attention
+//                         cache overwritten (whisper.rs:72-88, decoder.rs:149-151,272-275) -- reproduced as is.
+// All clips of one call must use the same mode.  tokens_out: [batch][224] (host), counts_out: [batch] (host).
+int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t batch, const int32_t *lang_tokens,
+                               int32_t *tokens_out, int32_t *counts_out, int32_t *detected_lang_out, wq4_stream stream)
+{
+    if (!m || !mel_dev || !lang_tokens || !tokens_out || !counts_out || batch <= 0) { wq4_set_error("wq4_whisper_transcribe: invalid argument"); return WQ4_ERR_INVALID; }
+    DeviceGuard g(m->device);
+    CHK(reserve(m, batch));
+    if (batch > m->max_batch) { wq4_set_error("wq4_whisper_transcribe: batch exceeds the reserved size"); return WQ4_ERR_INVALID; }
+    const int64_t B = batch;
+    cudaStream_t st = (cudaStream_t)stream;
+    const wq4_whisper_config &c = m->cfg;
+    const int SOT = 50258, EOT = 50257, MAX_TOKENS = 224, MIN_TOKENS = 3;   // whisper.rs:15-20,97
+    const int transcribe_tok = 50260 + c.n_lang, no_ts_tok = transcribe_tok + 4;   // config.rs:66-75
+    const bool autodetect = lang_tokens[0] < 0;
+    for (int64_t b = 0; b < B; b++)
+        if ((lang_tokens[b] < 0) != autodetect) { wq4_set_error("wq4_whisper_transcribe: mixed prompt modes in one batch"); return WQ4_ERR_INVALID; }
+
+    CHK(encode(m, mel_dev, B, st));
+    CHK(cross_kv(m, B, st));
+
+    std::vector<int> prompt;   // [B][q_len]
+    int64_t position = 0, q_len;
+    std::vector<int> langs((size_t)B);
+    if (!autodetect) {
+        q_len = 4;
+        prompt.resize((size_t)B * 4);
+        for (int64_t b = 0; b < B; b++) {
+            langs[b] = lang_tokens[b];
+            int *p = &prompt[(size_t)b * 4];
+            p[0] = SOT; p[1] = lang_tokens[b]; p[2] = transcribe_tok; p[3] = no_ts_tok;
+        }
+    } else {
+        std::vector<int> sot((size_t)B, SOT);
+        WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, sot.data(), B * 4, cudaMemcpyHostToDevice, st));
+        CHK(decoder_pass(m, B, 1, 0, 0, st));                              // whisper.rs:73
+        position = 1;
+        CHK(wq4m_argmax(m->logits, B, m->V, 50259, 50259 + c.n_lang, nullptr, m->d_next, st));   // whisper.rs:77-83
+        WQ4_CUDA(cudaMemcpyAsync(m->h_next, m->d_next, B * 4, cudaMemcpyDeviceToHost, st));
+        WQ4_CUDA(cudaStreamSynchronize(st));
+        q_len = 3;
+        prompt.resize((size_t)B * 3);
+        for (int64_t b = 0; b < B; b++) {
+            langs[b] = m->h_next[b];
+            int *p = &prompt[(size_t)b * 3];
+            p[0] = langs[b]; p[1] = transcribe_tok; p[2] = no_ts_tok;
+        }
+    }
+    if (detected_lang_out) for (int64_t b = 0; b < B; b++) detected_lang_out[b] = langs[b];
+    WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, prompt.data(), prompt.size() * 4, cudaMemcpyHostToDevice, st));
+    CHK(decoder_pass(m, B, q_len, 0, 0, st));                              // forward_prompt: positions restart at 0
+    position += q_len;                                                     // whisper.rs:93
+    int64_t kv_len = q_len;                                                // cache now holds the prompt only
+    CHK(wq4m_argmax(m->logits, B, m->V, 0, m->V, m->d_sup_eot, m->d_next, st));   // whisper.rs:98-99
+
+    std::vector<int> count((size_t)B, 0);
+    std::vector<char> done((size_t)B, 0);
+    for (int step = 0; step < MAX_TOKENS; step++) {                        // whisper.rs:104-125
+        WQ4_CUDA(cudaMemcpyAsync(m->h_next, m->d_next, B * 4, cudaMemcpyDeviceToHost, st));
+        WQ4_CUDA(cudaStreamSynchronize(st));
+        bool all_done = true;
+        for (int64_t b = 0; b < B; b++) {
+            if (done[b]) continue;
+            int tok = m->h_next[b];
+            if (tok == EOT) { done[b] = 1; continue; }
+            tokens_out[(size_t)b * MAX_TOKENS + count[b]++] = tok;
+            all_done = false;
+        }
+        if (all_done) break;
+        if (step == MAX_TOKENS - 1) break;   // the reference computes one more step whose result it never uses
+        if (position >= c.n_text_ctx || kv_len >= c.n_text_ctx) break;
+        WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, m->d_next, B * 4, cudaMemcpyDeviceToDevice, st));
+        CHK(decoder_pass(m, B, 1, position, kv_len, st));                  // whisper.rs:116
+        position += 1;
+        kv_len += 1;
+        const int *sup = (step + 1 < MIN_TOKENS) ? m->d_sup_eot : m->d_sup_none;   // whisper.rs:120-122
+        CHK(wq4m_argmax(m->logits, B, m->V, 0, m->V, sup, m->d_next, st));
+    }
+    for (int64_t b = 0; b < B; b++) counts_out[b] = count[b];
+    return WQ4_OK;
+}
+
+// GGUF reader probes (host only, no device needed): GgufReader::{version, tensor_count, tensor_info,
+// tensor_data} (reader.rs:190-223).
+int32_t wq4_gguf_probe(const uint8_t *data, size_t nbytes, uint32_t *version, uint64_t *tensor_count, uint64_t *data_offset)
+{
+    if (!data) { wq4_set_error("wq4_gguf_probe: null data"); return WQ4_ERR_INVALID; }
+    Gguf g;
+    if (!g.parse(data, nbytes)) { wq4_set_error("Failed to parse GGUF: %s", g.err.c_str()); return WQ4_ERR_INVALID; }
+    if (version) *version = g.version;
+    if (tensor_count) *tensor_count = g.tensor_count;
+    if (data_offset) *data_offset = g.data_offset;
+    return WQ4_OK;
+}
+
+int32_t wq4_gguf_tensor_info(const uint8_t *data, size_t nbytes, const char *name, uint64_t *dims4, uint32_t *ndims,
+                             uint32_t *dtype, uint64_t *abs_offset, uint64_t *byte_size)
+{
+    if (!data || !name) { wq4_set_error("wq4_gguf_tensor_info: null argument"); return WQ4_ERR_INVALID; }
+    Gguf g;
+    if (!g.parse(data, nbytes)) { wq4_set_error("Failed to parse GGUF: %s", g.err.c_str()); return WQ4_ERR_INVALID; }
+    const GgufTensor *t = g.find(name);
+    if (!t) { wq4_set_error("Tensor '%s' not found in GGUF", name); return WQ4_ERR_INVALID; }
+    if (ndims) *ndims = (uint32_t)t->dims.size();
+    if (dims4) for (size_t i = 0; i < 4; i++) dims4[i] = i < t->dims.size() ? t->dims[i] : 1;
+    if (dtype) *dtype = t->dtype;
+    if (abs_offset) *abs_offset = g.data_offset + t->offset;
+    if (byte_size) *byte_size = t->byte_size();
+    if (!g.tensor_data(*t)) { wq4_set_error("Tensor '%s' data out of range", name); return WQ4_ERR_BYTES; }
+    return WQ4_OK;
+}
+
+// Test / bench hooks ------------------------------------------------------------------------------
+// Runs the cross-K/V projection and ONE decoder pass with caller-given tokens; copies the logits out.
+int32_t wq4_whisper_decoder_pass(wq4_whisper *m, const int32_t *tokens_host, int64_t batch, int64_t q_len, int64_t emb_pos0,
+                                 int64_t kv_pos0, int32_t recompute_cross, float *logits_dev, wq4_stream stream)
+{
+    if (!m || !tokens_host || batch <= 0 || q_len <= 0) { wq4_set_error("wq4_whisper_decoder_pass: invalid argument"); return WQ4_ERR_INVALID; }
+    DeviceGuard g(m->device);
+    if (batch > m->max_batch) { wq4_set_error("wq4_whisper_decoder_pass: call wq4_whisper_encode first"); return WQ4_ERR_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (recompute_cross) CHK(cross_kv(m, batch, st));
+    WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, tokens_host, (size_t)batch * q_len * 4, cudaMemcpyHostToDevice, st));
+    CHK(decoder_pass(m, batch, q_len, emb_pos0, kv_pos0, st));
+    if (logits_dev) WQ4_CUDA(cudaMemcpyAsync(logits_dev, m->logits, (size_t)batch * m->V * 4, cudaMemcpyDeviceToDevice, st));
+    return WQ4_OK;
+}
+
+// Stream-ordered single decode step on device-resident tokens (CUDA-graph capturable; used by bench.py):
+// consumes d_next of the previous step, leaves the greedy pick in d_next again.
+int32_t wq4_whisper_decode_step_device(wq4_whisper *m, int64_t batch, int64_t position, int64_t kv_len, wq4_stream stream)
+{
+    if (!m || batch <= 0 || batch > m->max_batch) { wq4_set_error("wq4_whisper_decode_step_device: invalid argument"); return WQ4_ERR_INVALID; }
+    DeviceGuard g(m->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, m->d_next, (size_t)batch * 4, cudaMemcpyDeviceToDevice, st));
+    CHK(decoder_pass(m, batch, 1, position, kv_len, st));
+    return wq4m_argmax(m->logits, batch, m->V, 0, m->V, m->d_sup_none, m->d_next, st);
+}
+
+}  // extern "C"
