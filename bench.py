@@ -189,8 +189,10 @@ def run_own(args):
     L = wb.lib()
     cfg = preset(args.model)
     B = args.batch
+    # encoder-only checkpoint: the decoder stack is not part of this workload, so it is neither generated nor loaded
+    import dataclasses
     blob = random_whisper_gguf(cfg, seed=0, with_decoder=False)
-    model = wb.load_whisper_from_gguf(blob, cfg, dev)
+    model = wb.load_whisper_from_gguf(blob, dataclasses.replace(cfg, n_text_layer=0), dev)
     del blob
     model.reserve(B)
     rng = np.random.default_rng(100 + rank)
