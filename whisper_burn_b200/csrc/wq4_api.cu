@@ -179,6 +179,16 @@ int32_t wq4_launch_cvt_f32_to_16(const float *src, void *dst, int64_t n, bool bf
 }
 
 // ---- dispatch -----------------------------------------------------------------------------------
+int wq4_gemm_impl()
+{
+    static int impl = -1;
+    if (impl < 0) {
+        const char *e = getenv("WQ4_GEMM_IMPL");
+        impl = (e && atoi(e) == 1) ? 1 : 2;
+    }
+    return impl;
+}
+
 static bool use_gemv(int64_t rows, uint32_t flags, bool has_f32_x)
 {
     if (flags & WQ4_FORCE_GEMM) return false;
@@ -261,7 +271,7 @@ int32_t wq4_linear_plan(const wq4_tensor *w, int64_t rows, uint32_t flags, int32
         if (tile_m) *tile_m = 0;
         return 0;
     }
-    if (tile_m) *tile_m = wq4_pick_tile_m(rows, w->np);
+    if (tile_m) *tile_m = wq4_gemm_impl() == 2 ? wq4_pick_tile_m2(rows, w->np_alloc / 2) : wq4_pick_tile_m(rows, w->np);
     return 1;
 }
 
@@ -294,6 +304,7 @@ int32_t wq4_linear_forward_ex(const wq4_tensor *w, const float *bias_dev, const 
     bool gemv = use_gemv(rows, flags, x_f32_dev != nullptr);
     if ((flags & WQ4_FORCE_GEMV) && rows <= 8 && x_f32_dev) gemv = true;
     if (gemv) return wq4_launch_gemv(a);
+    if (wq4_gemm_impl() == 2) return wq4_launch_gemm2_q4(a, wq4_pick_tile_m2(rows, w->np_alloc / 2));
     return wq4_launch_gemm_q4(a, wq4_pick_tile_m(rows, w->np));
 }
 

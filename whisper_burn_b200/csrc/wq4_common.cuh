@@ -7,7 +7,7 @@
 //   nib[p][kb][r] : uint4   16 bytes = the 32 nibbles of block (row = 128*p + r, kb)
 //   scl[p][kb][r] : __half  the block's f16 scale, bit-identical to the GGUF scale
 //
-// with p < NP = ceil(rows/128), kb < KBP = round_up(K/32, 2), r < 128.  A (panel, kb) slab of
+// with p < NP = ceil(rows/128), kb < KBP = round_up(K/32, 4), r < 128.  A (panel, kb) slab of
 // 128 blocks is 2 KiB contiguous, so one warp reads 512 contiguous bytes and one K-stage of
 // the GEMM (two kb) is a single 4 KiB bulk copy.  Padding rows / padding kb carry scale 0 and
 // nibble 8.  Within a block, 32-bit word c (0..3) holds elements 8c..8c+7; element 8c+j sits
@@ -36,8 +36,9 @@ struct wq4_tensor {
     int64_t num_blocks;    // n*k/32
     int64_t rows;          // matrix mode: n ; flat mode (k % 32 != 0): num_blocks
     int64_t kb;            // blocks per row: k/32 ; flat mode: 1
-    int64_t kbp;           // kb rounded up to a multiple of 2
+    int64_t kbp;           // kb rounded up to a multiple of 4
     int64_t np;            // ceil(rows/128)
+    int64_t np_alloc;      // np rounded up to even: the CTA-pair GEMM always works on two panels (padding: scale 0)
     int matrix_mode;       // 1 when k % 32 == 0 (matmul allowed)
     int device;
     uint4 *nib;            // [np][kbp][128]
@@ -116,6 +117,10 @@ struct LinearArgs {
 int32_t wq4_launch_gemv(const LinearArgs &a);
 int32_t wq4_launch_gemm_q4(const LinearArgs &a, int tile_m);
 int wq4_pick_tile_m(int64_t rows, int64_t np);
+// second-generation Q4 GEMM (CTA pair, A operand in tensor memory; wq4_gemm2.cu)
+int32_t wq4_launch_gemm2_q4(const LinearArgs &a, int tile_m);
+int wq4_pick_tile_m2(int64_t rows, int64_t npairs);
+int wq4_gemm_impl();   // 2 (default) or 1 (WQ4_GEMM_IMPL=1: first-generation kernel, kept for A/B runs)
 int wq4_gemm_cluster_size(int64_t np);
 
 // Tensor-core GEMM on a dense 16-bit weight (the Conv1D stem).  The activation operand is a

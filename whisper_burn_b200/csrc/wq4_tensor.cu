@@ -135,9 +135,10 @@ int32_t wq4_tensor_create(const uint8_t *host_blocks, size_t nbytes, int64_t n, 
     t->matrix_mode = (k % 32 == 0) ? 1 : 0;
     t->rows = t->matrix_mode ? n : num_blocks;
     t->kb = t->matrix_mode ? k / 32 : 1;
-    t->kbp = (t->kb + 1) / 2 * 2;
+    t->kbp = (t->kb + 3) / 4 * 4;   // one K stage of the CTA-pair GEMM is four k-blocks (128 elements)
     t->np = (t->rows + WQ4_PANEL_ROWS - 1) / WQ4_PANEL_ROWS;
-    int64_t entries = t->np * t->kbp * WQ4_PANEL_ROWS;
+    t->np_alloc = (t->np + 1) / 2 * 2;
+    int64_t entries = t->np_alloc * t->kbp * WQ4_PANEL_ROWS;
     t->nib = nullptr; t->scl = nullptr;
     uint8_t *staging = nullptr;
     cudaError_t e;
