@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cuda_fp16.h>
+struct wq4_tensor;
 
 int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y32, void *y16, int64_t rows, int64_t D,
                        cudaStream_t st);
@@ -18,3 +20,46 @@ int32_t wq4m_argmax(const float *logits, int64_t nb, int64_t V, int64_t lo, int6
                     cudaStream_t st);
 int32_t wq4m_kv_append(const float *qkv, int64_t ld_src, void *kc, void *vc, int64_t ldkv, int64_t kv_batch_stride, int64_t B,
                        int64_t D, int64_t q_len, int64_t pos0, cudaStream_t st);
+
+// ---- decode-step megakernel (wq4_decode.cu) ------------------------------------------------------------
+// Decode-layout Q4 weight: rows are dealt to the CTAs of the persistent decode kernel in contiguous ranges of
+// `rpc` rows; CTA c's chunk is nib[c][kb][rpc] (uint4 = one 32-weight block, same nibble interleave as the
+// panel layout) and scl[c][kb][rpc] (f16, bit-identical GGUF scales).  Rows >= n inside the last chunk carry
+// scale 0.  Same 18 bytes per block as GGUF.
+struct DecWeight {
+    const uint4 *nib;
+    const __half *scl;
+    const float *bias;   // [n] or null
+    int n, k, kb, rpc;
+};
+struct DecLayerW {
+    const float *ln1w, *ln1b, *ln2w, *ln2b, *ln3w, *ln3b;
+    DecWeight qkv, out, cq, cout, fc1, fc2;
+};
+struct DecodeStepArgs {
+    const DecLayerW *layers;      // device array [n_layers]
+    int n_layers, B, D, F, H, V, ctx, T_enc;
+    const int *tokens;            // [B] device
+    const float *tok_emb;         // [V][D] f32 (embedding lookup)
+    const __half *tok_emb16;      // [V][D] f16 (logits matrix)
+    const float *pos_emb;         // [ctx][D]
+    int emb_pos;                  // positional row of this step
+    int kv_len;                   // self-attention cache rows valid BEFORE this step (the new row is written at kv_len)
+    float *x, *q, *h, *part;      // [B][D], [B][D], [B][F], attention partials
+    __half *self_k, *self_v;      // [L][B][ctx][D]
+    const __half *cross_kv;       // [L][B*T_enc][2D]
+    const float *lnfw, *lnfb;
+    float *logits;                // [B][V]
+    int arg_lo, arg_hi;           // greedy pick over [lo, hi); arg_hi <= arg_lo: no pick
+    const int *suppress;          // [B] token to exclude (-1 none) or null
+    int *next_out;                // [B]
+    float *arg_scratch;           // [grid][B][2]
+    unsigned *barrier;            // grid barrier counter (zeroed before every launch)
+    int *dev_err;
+};
+// Builds the decode layout of a panel-layout tensor (device to device).
+int32_t wq4m_decw_create(const wq4_tensor *t, const float *bias_dev, int n_cta, DecWeight *out, void **alloc_nib, void **alloc_scl,
+                         cudaStream_t st);
+int wq4m_decode_grid(int device);
+int32_t wq4m_decode_step(const DecodeStepArgs &a, int device, cudaStream_t st);
+int32_t wq4m_cvt_f32_f16(const float *src, void *dst, int64_t n, cudaStream_t st);

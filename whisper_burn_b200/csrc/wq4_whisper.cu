@@ -157,6 +157,13 @@ struct wq4_whisper {
     void *lin_ws = nullptr;
     size_t lin_ws_bytes = 0;
     int64_t max_q = 8;               // rows per batch item in one decoder call (prompt <= 4 tokens)
+    // decode-step megakernel state (wq4_decode.cu): decode-layout copies of the decoder linears, f16 logits matrix
+    std::vector<DecLayerW> dec_w_host;
+    DecLayerW *dec_w_dev = nullptr;
+    __half *tok_emb16 = nullptr;
+    float *att_part = nullptr, *arg_scratch = nullptr;
+    unsigned *grid_bar = nullptr;
+    bool decode_kernel_ready = false;
 };
 
 namespace {
@@ -361,6 +368,34 @@ int32_t reserve(wq4_whisper *m, int64_t B)
     WQ4_CUDA(cudaMallocHost(&m->h_next, (size_t)B * 4));
     m->lin_ws_bytes = (size_t)R * (size_t)F * 2 + 4096;   // f32 -> f16 copy of the widest decoder activation
     CHK(dev_alloc(m, reinterpret_cast<uint8_t **>(&m->lin_ws), m->lin_ws_bytes));
+    // decode-step megakernel: decode-layout weights (rows dealt to one CTA per SM), f16 logits matrix, scratch
+    if (!m->dec.empty()) {
+        const int n_cta = wq4m_decode_grid(m->device);
+        m->dec_w_host.resize(m->dec.size());
+        auto mk = [&](const Lin &l, DecWeight *out) -> int32_t {
+            void *a1 = nullptr, *a2 = nullptr;
+            CHK(wq4m_decw_create(l.w, l.bias, n_cta, out, &a1, &a2, nullptr));
+            m->owned.push_back(a1); m->owned.push_back(a2);
+            return WQ4_OK;
+        };
+        for (size_t l = 0; l < m->dec.size(); l++) {
+            DecLayer &L = m->dec[l];
+            DecLayerW &W = m->dec_w_host[l];
+            W.ln1w = L.attn_ln.w; W.ln1b = L.attn_ln.b; W.ln2w = L.cross_ln.w; W.ln2b = L.cross_ln.b;
+            W.ln3w = L.mlp_ln.w; W.ln3b = L.mlp_ln.b;
+            CHK(mk(L.qkv, &W.qkv)); CHK(mk(L.out, &W.out)); CHK(mk(L.cq, &W.cq)); CHK(mk(L.cout, &W.cout));
+            CHK(mk(L.fc1, &W.fc1)); CHK(mk(L.fc2, &W.fc2));
+        }
+        CHK(dev_alloc(m, &m->dec_w_dev, m->dec.size()));
+        WQ4_CUDA(cudaMemcpy(m->dec_w_dev, m->dec_w_host.data(), m->dec.size() * sizeof(DecLayerW), cudaMemcpyHostToDevice));
+        CHK(dev_alloc(m, &m->tok_emb16, (size_t)m->V * D));
+        CHK(wq4m_cvt_f32_f16(m->tok_emb, m->tok_emb16, m->V * D, nullptr));
+        CHK(dev_alloc(m, &m->att_part, (size_t)8 * m->cfg.n_text_head * 8 * 66));
+        CHK(dev_alloc(m, &m->arg_scratch, (size_t)n_cta * 8 * 2));
+        CHK(dev_alloc(m, &m->grid_bar, 4));
+        WQ4_CUDA(cudaDeviceSynchronize());
+        m->decode_kernel_ready = true;
+    }
     m->max_batch = B;
     return WQ4_OK;
 }
@@ -424,8 +459,39 @@ int32_t cross_kv(wq4_whisper *m, int64_t B, cudaStream_t st)
 // One decoder pass over q_len new positions per clip (forward_prompt / decode_step, decoder.rs:251-348).
 //   emb_pos0 : first positional-embedding row;  kv_pos0 : self-attention cache rows already valid
 //   (the prompt pass overwrites from 0, decoder.rs:149-151).  Leaves logits of the LAST position.
-int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, cudaStream_t st)
+struct ArgReq { int lo, hi; const int *suppress; int *out; };
+
+static bool use_decode_kernel()
 {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("WQ4_DECODE_IMPL"); v = (e && atoi(e) == 1) ? 0 : 1; }   // 1 = per-op launches (A/B runs)
+    return v == 1;
+}
+
+// One decode step for B <= 8 clips as a single persistent kernel (wq4_decode.cu).
+int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
+{
+    DecodeStepArgs a = {};
+    a.layers = m->dec_w_dev; a.n_layers = (int)m->dec.size(); a.B = (int)B; a.D = (int)m->D; a.F = (int)m->F;
+    a.H = m->cfg.n_text_head; a.V = (int)m->V; a.ctx = m->cfg.n_text_ctx; a.T_enc = (int)m->T_enc;
+    a.tokens = m->d_tokens; a.tok_emb = m->tok_emb; a.tok_emb16 = m->tok_emb16; a.pos_emb = m->dec_pos;
+    a.emb_pos = (int)emb_pos; a.kv_len = (int)kv_pos0;
+    a.x = m->dx; a.q = m->dq; a.h = m->dh; a.part = m->att_part;
+    a.self_k = m->self_k; a.self_v = m->self_v; a.cross_kv = m->cross_kv;
+    a.lnfw = m->ln.w; a.lnfb = m->ln.b; a.logits = m->logits;
+    a.arg_lo = arg ? arg->lo : 0; a.arg_hi = arg ? arg->hi : 0; a.suppress = arg ? arg->suppress : nullptr;
+    a.next_out = arg ? arg->out : nullptr; a.arg_scratch = m->arg_scratch; a.barrier = m->grid_bar;
+    a.dev_err = wq4_error_flag_ptr(m->device);
+    if (!a.dev_err) return WQ4_ERR_CUDA;
+    return wq4m_decode_step(a, m->device, st);
+}
+
+int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
+{
+    if (q_len == 1 && B <= 8 && m->decode_kernel_ready && use_decode_kernel()) {
+        if (kv_pos0 + 1 > m->cfg.n_text_ctx || emb_pos0 + 1 > m->cfg.n_text_ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
+        return decode_step_fused(m, B, emb_pos0, kv_pos0, arg, st);
+    }
     const int64_t D = m->D, F = m->F, R = B * q_len, ctx = m->cfg.n_text_ctx, H = m->cfg.n_text_head;
     const int64_t M = B * m->T_enc;
     if (q_len > m->max_q || kv_pos0 + q_len > ctx || emb_pos0 + q_len > ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
@@ -461,7 +527,9 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
     }
     const float *last = q_len == 1 ? m->dxn : m->dq;
     (void)F;
-    return wq4m_logits(last, m->tok_emb, m->logits, B, D, m->V, st);
+    CHK(wq4m_logits(last, m->tok_emb, m->logits, B, D, m->V, st));
+    if (arg && arg->hi > arg->lo) CHK(wq4m_argmax(m->logits, B, m->V, arg->lo, arg->hi, arg->suppress, arg->out, st));
+    return WQ4_OK;
 }
 
 }  // namespace
@@ -613,9 +681,9 @@ int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t bat
     } else {
         std::vector<int> sot((size_t)B, SOT);
         WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, sot.data(), B * 4, cudaMemcpyHostToDevice, st));
-        CHK(decoder_pass(m, B, 1, 0, 0, st));                              // whisper.rs:73
+        ArgReq lang_req = {50259, 50259 + c.n_lang, nullptr, m->d_next};      // whisper.rs:77-83
+        CHK(decoder_pass(m, B, 1, 0, 0, &lang_req, st));                   // whisper.rs:73
         position = 1;
-        CHK(wq4m_argmax(m->logits, B, m->V, 50259, 50259 + c.n_lang, nullptr, m->d_next, st));   // whisper.rs:77-83
         WQ4_CUDA(cudaMemcpyAsync(m->h_next, m->d_next, B * 4, cudaMemcpyDeviceToHost, st));
         WQ4_CUDA(cudaStreamSynchronize(st));
         q_len = 3;
@@ -628,10 +696,10 @@ int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t bat
     }
     if (detected_lang_out) for (int64_t b = 0; b < B; b++) detected_lang_out[b] = langs[b];
     WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, prompt.data(), prompt.size() * 4, cudaMemcpyHostToDevice, st));
-    CHK(decoder_pass(m, B, q_len, 0, 0, st));                              // forward_prompt: positions restart at 0
+    ArgReq first_req = {0, (int)m->V, m->d_sup_eot, m->d_next};            // whisper.rs:98-99
+    CHK(decoder_pass(m, B, q_len, 0, 0, &first_req, st));                  // forward_prompt: positions restart at 0
     position += q_len;                                                     // whisper.rs:93
     int64_t kv_len = q_len;                                                // cache now holds the prompt only
-    CHK(wq4m_argmax(m->logits, B, m->V, 0, m->V, m->d_sup_eot, m->d_next, st));   // whisper.rs:98-99
 
     std::vector<int> count((size_t)B, 0);
     std::vector<char> done((size_t)B, 0);
@@ -650,11 +718,11 @@ int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t bat
         if (step == MAX_TOKENS - 1) break;   // the reference computes one more step whose result it never uses
         if (position >= c.n_text_ctx || kv_len >= c.n_text_ctx) break;
         WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, m->d_next, B * 4, cudaMemcpyDeviceToDevice, st));
-        CHK(decoder_pass(m, B, 1, position, kv_len, st));                  // whisper.rs:116
+        const int *sup = (step + 1 < MIN_TOKENS) ? m->d_sup_eot : m->d_sup_none;   // whisper.rs:120-122
+        ArgReq req = {0, (int)m->V, sup, m->d_next};
+        CHK(decoder_pass(m, B, 1, position, kv_len, &req, st));            // whisper.rs:116
         position += 1;
         kv_len += 1;
-        const int *sup = (step + 1 < MIN_TOKENS) ? m->d_sup_eot : m->d_sup_none;   // whisper.rs:120-122
-        CHK(wq4m_argmax(m->logits, B, m->V, 0, m->V, sup, m->d_next, st));
     }
     for (int64_t b = 0; b < B; b++) counts_out[b] = count[b];
     return WQ4_OK;
@@ -701,7 +769,7 @@ int32_t wq4_whisper_decoder_pass(wq4_whisper *m, const int32_t *tokens_host, int
     cudaStream_t st = (cudaStream_t)stream;
     if (recompute_cross) CHK(cross_kv(m, batch, st));
     WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, tokens_host, (size_t)batch * q_len * 4, cudaMemcpyHostToDevice, st));
-    CHK(decoder_pass(m, batch, q_len, emb_pos0, kv_pos0, st));
+    CHK(decoder_pass(m, batch, q_len, emb_pos0, kv_pos0, nullptr, st));
     if (logits_dev) WQ4_CUDA(cudaMemcpyAsync(logits_dev, m->logits, (size_t)batch * m->V * 4, cudaMemcpyDeviceToDevice, st));
     return WQ4_OK;
 }
@@ -714,8 +782,8 @@ int32_t wq4_whisper_decode_step_device(wq4_whisper *m, int64_t batch, int64_t po
     DeviceGuard g(m->device);
     cudaStream_t st = (cudaStream_t)stream;
     WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, m->d_next, (size_t)batch * 4, cudaMemcpyDeviceToDevice, st));
-    CHK(decoder_pass(m, batch, 1, position, kv_len, st));
-    return wq4m_argmax(m->logits, batch, m->V, 0, m->V, m->d_sup_none, m->d_next, st);
+    ArgReq req = {0, (int)m->V, m->d_sup_none, m->d_next};
+    return decoder_pass(m, batch, 1, position, kv_len, &req, st);
 }
 
 }  // extern "C"
