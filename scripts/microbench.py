@@ -85,16 +85,18 @@ def bench_gemv(rows, n, k, reps=64):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--rows", default="", help="comma-separated GEMM row counts (default 1500,6000,48000)")
+    ap.add_argument("--no-gemv", action="store_true")
     a = ap.parse_args()
     shapes = [(1280, 1280), (5120, 1280), (1280, 5120), (3840, 1280), (1024, 1024), (4096, 1024), (1024, 4096)]
     print("-- GEMM, f16 activations resident, CUDA-graph replay, weights rotate through >L2 --")
-    for rows in ((1500,) if a.quick else (1500, 6000, 48000)):
+    for rows in (tuple(int(r) for r in a.rows.split(',')) if a.rows else (1500,) if a.quick else (1500, 6000, 48000)):
         for n, k in shapes:
             dt, tile = bench_gemm(rows, n, k, reps=20 if rows < 20000 else 6)
             print(f"rows {rows:6d} N {n:5d} K {k:5d} tile_m {tile:3d}: {dt*1e6:9.1f} us {2*rows*n*k/dt/1e12:8.1f} TFLOP/s "
                   f"({2*rows*n*k/dt/1e12/1679*100:5.1f}% of measured 1679)", flush=True)
     print("-- GEMV, f32, CUDA-graph replay --")
-    for rows in (1, 4, 8):
+    for rows in (() if a.no_gemv else (1, 4, 8)):
         for n, k in shapes:
             dt = bench_gemv(rows, n, k)
             by = n * k // 32 * 18 + 4 * k * rows + 4 * n + 4 * n * rows

@@ -31,8 +31,9 @@ namespace {
 
 constexpr int kDT = 512;          // threads per CTA
 constexpr int kMaxR = 8;          // clips per launch
-constexpr int kPartStride = 66;   // (m, l, o[64]) per attention partial
-constexpr int kMaxSplit = 8;
+constexpr int kPartStride = 68;   // o[64], m, l, pad (16-byte aligned rows) per attention partial
+constexpr int kMaxSeg = 4;        // units a CTA's key range may touch
+constexpr int kMaxParts = 10;     // partials per unit
 
 __device__ __forceinline__ uint4 ldg_stream16(const uint4 *p)
 {
@@ -68,7 +69,8 @@ __device__ __forceinline__ uint16_t f32_to_f16_sat_d(float v)
 
 // Grid-wide barrier over a monotonically increasing counter (zeroed by the host before each launch).
 // Bounded: a co-residency or logic bug raises the device error flag instead of hanging the GPU.
-__device__ __forceinline__ void grid_barrier(unsigned *counter, unsigned &target, int *dev_err)
+// `timeline` (normally NULL) receives CTA 0's %globaltimer after barrier i at slot i: scripts/decode_timeline.py.
+__device__ __forceinline__ void grid_barrier(unsigned *counter, unsigned &target, int *dev_err, long long *timeline)
 {
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -78,6 +80,12 @@ __device__ __forceinline__ void grid_barrier(unsigned *counter, unsigned &target
         unsigned spins = 0;
         while (ld_acquire_u32(counter) < target) {
             if (++spins > (1u << 24)) { atomicCAS(dev_err, 0, 301); break; }
+        }
+        if (timeline && blockIdx.x == 0) {
+            const unsigned slot = target / gridDim.x - 1;
+            long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (slot < (unsigned)kDecTimelineSlots) timeline[slot] = t;
         }
     }
     __syncthreads();
@@ -101,22 +109,26 @@ __device__ __forceinline__ void word_to_f32(uint32_t w, float (&f)[8])
     f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
 }
 
-// acc[m] += d * sum_k (nib - 8) * xs[m][kbi*32 + k]   for one block
+// acc[m] += d * sum_k (nib - 8) * xs[m][kbi*32 + k]   for one block.
+// The word loop is deliberately NOT unrolled: every phase of the persistent kernel executes its code once per
+// layer, so straight-line code is fetched cold from L2 each time; a compact loop body keeps the instruction
+// stream of a phase within the instruction cache (the fully unrolled R = 8 body was 24 KB and fetch bound).
 template <int R>
-__device__ __forceinline__ void block_dot(const uint4 &q, float d, const float *xs, int K, int kbi, float (&acc)[R])
+__device__ __forceinline__ void block_dot(uint4 q, float d, const float *xs, int K, int kbi, float (&acc)[R])
 {
     float bs[R];
 #pragma unroll
     for (int m = 0; m < R; m++) bs[m] = 0.0f;
-    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
+    const float *xp = xs + kbi * 32;
+#pragma unroll 1
     for (int c = 0; c < 4; c++) {
         float f[8];
-        word_to_f32(w[c], f);
+        word_to_f32(q.x, f);
+        q.x = q.y; q.y = q.z; q.z = q.w;
 #pragma unroll
         for (int m = 0; m < R; m++) {
-            const float4 xa = *reinterpret_cast<const float4 *>(xs + (size_t)m * K + kbi * 32 + c * 8);
-            const float4 xb = *reinterpret_cast<const float4 *>(xs + (size_t)m * K + kbi * 32 + c * 8 + 4);
+            const float4 xa = *reinterpret_cast<const float4 *>(xp + (size_t)m * K + c * 8);
+            const float4 xb = *reinterpret_cast<const float4 *>(xp + (size_t)m * K + c * 8 + 4);
             float s = bs[m];
             s = fmaf(f[0], xa.x, s); s = fmaf(f[1], xa.y, s); s = fmaf(f[2], xa.z, s); s = fmaf(f[3], xa.w, s);
             s = fmaf(f[4], xb.x, s); s = fmaf(f[5], xb.y, s); s = fmaf(f[6], xb.z, s); s = fmaf(f[7], xb.w, s);
@@ -130,8 +142,30 @@ __device__ __forceinline__ void block_dot(const uint4 &q, float d, const float *
 // One GEMV phase: y[m][n] = epi(sum_k W[n][k] xs[m][k] + bias[n]) for this CTA's rows.
 //   xs  : shared memory, f32 [R][K]
 //   red : shared memory scratch, >= kDT * R floats
-template <int R, class Epi>
-__device__ __forceinline__ void gemv_phase(const DecWeight &w, const float *xs, float *red, int nrows, Epi epi)
+// Epilogue of a GEMV phase (selected at run time so one copy of the GEMV code serves all six linears).
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_GELU = 2, EPI_QKV = 3 };
+struct EpiCtx {
+    int kind;
+    float *dst;        // STORE/GELU/QKV(q): dst[m*ld + n] ; RESID: dst[m*ld + n] += v
+    int ld;
+    __half *sk, *sv;   // QKV: f16 cache rows (clip stride ctx*D), row kvrow
+    int ctx, kvrow, D;
+};
+__device__ __forceinline__ void epi_apply(const EpiCtx &e, int m, int n, float v)
+{
+    if (e.kind == EPI_STORE) e.dst[(size_t)m * e.ld + n] = v;
+    else if (e.kind == EPI_RESID) e.dst[(size_t)m * e.ld + n] = v;   // residual already added by the caller
+    else if (e.kind == EPI_GELU) e.dst[(size_t)m * e.ld + n] = wq4_gelu_tanh(v);
+    else {
+        const int D = e.D;
+        if (n < D) e.dst[(size_t)m * e.ld + n] = v;
+        else if (n < 2 * D) e.sk[((size_t)m * e.ctx + e.kvrow) * D + (n - D)] = __ushort_as_half(f32_to_f16_sat_d(v));
+        else e.sv[((size_t)m * e.ctx + e.kvrow) * D + (n - 2 * D)] = __ushort_as_half(f32_to_f16_sat_d(v));
+    }
+}
+
+template <int R>
+__device__ __noinline__ void gemv_phase(const DecWeight w, const float *xs, float *red, int nrows, const EpiCtx epi)
 {
     const int tid = threadIdx.x;
     const int rpc = w.rpc, kb = w.kb, K = w.k;
@@ -140,6 +174,21 @@ __device__ __forceinline__ void gemv_phase(const DecWeight &w, const float *xs, 
     if (KL > kb) KL = kb;
     const int kl = tid / rpc, slot = tid - kl * rpc;
     const bool active = kl < KL && row0 < w.n;
+    // the bias of the outputs this thread will finish (four lanes per output, see below), loaded before the
+    // weight stream so its latency is hidden
+    float bias_pre[3];       // + the residual value for EPI_RESID (x += ...), so the epilogue has no dependent load
+    {
+        const int g4 = tid >> 2;
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            const int o = i * (kDT / 4) + g4;
+            const int s2 = o / R, m = o - s2 * R, n = row0 + s2;
+            const bool ok = o < rpc * R && n < w.n && m < nrows;
+            float v = (w.bias && ok) ? __ldg(w.bias + n) : 0.0f;
+            if (epi.kind == EPI_RESID && ok) v += __ldcg(epi.dst + (size_t)m * epi.ld + n);
+            bias_pre[i] = v;
+        }
+    }
     float acc[R];
 #pragma unroll
     for (int m = 0; m < R; m++) acc[m] = 0.0f;
@@ -151,70 +200,126 @@ __device__ __forceinline__ void gemv_phase(const DecWeight &w, const float *xs, 
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const int kbi = kb0 + u * KL;
+                q[u] = make_uint4(0, 0, 0, 0); d[u] = 0.0f;
                 if (kbi < kb) {
                     q[u] = ldg_stream16(w.nib + cbase + (size_t)kbi * rpc);
                     d[u] = __half2float(__ldg(w.scl + cbase + (size_t)kbi * rpc));
                 }
             }
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
+#pragma unroll 1
+            for (int u = 0; u < 4; u++) {                 // compact loop: rotate the four prefetched blocks
                 const int kbi = kb0 + u * KL;
-                if (kbi < kb) block_dot<R>(q[u], d[u], xs, K, kbi, acc);
+                if (kbi < kb) block_dot<R>(q[0], d[0], xs, K, kbi, acc);
+                q[0] = q[1]; q[1] = q[2]; q[2] = q[3];
+                d[0] = d[1]; d[1] = d[2]; d[2] = d[3];
             }
         }
 #pragma unroll
         for (int m = 0; m < R; m++) red[(kl * rpc + slot) * R + m] = acc[m];
     }
     __syncthreads();
-    for (int t = tid; t < rpc * R; t += kDT) {
-        const int s2 = t / R, m = t - s2 * R;
+    // four lanes per output: strided partial sums, then two shuffles (fixed order: deterministic)
+    const int g4 = tid >> 2, sub = tid & 3;
+    int it = 0;
+    for (int o0 = 0; o0 < rpc * R; o0 += kDT / 4, it++) {      // uniform trip count (shuffles inside)
+        const int o = o0 + g4;
+        const bool ok = o < rpc * R;
+        const int s2 = ok ? o / R : 0, m = ok ? o - s2 * R : 0;
+        float s = 0.0f;
+        if (ok) for (int l = sub; l < KL; l += 4) s += red[(l * rpc + s2) * R + m];
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
         const int n = row0 + s2;
-        if (n < w.n && m < nrows) {
-            float s = 0.0f;
-            for (int l = 0; l < KL; l++) s += red[(l * rpc + s2) * R + m];   // fixed order: deterministic
-            if (w.bias) s += w.bias[n];
-            epi(m, n, s);
+        if (ok && sub == 0 && n < w.n && m < nrows) {
+            if (it < 3) s += bias_pre[it];
+            else { if (w.bias) s += w.bias[n]; if (epi.kind == EPI_RESID) s += __ldcg(epi.dst + (size_t)m * epi.ld + n); }
+            epi_apply(epi, m, n, s);
         }
     }
     __syncthreads();
 }
 
 // LayerNorm::forward (src/model/layers.rs:23-31) of R rows of a global [R][D] f32 matrix into shared memory.
-// Warp m handles row m.  The rows were written by other CTAs in an earlier phase: read through L2 (ld.cg).
+// kDT/R threads per row issue all their loads at once (one L2 round trip); two block-wide reductions through
+// `red`.  The rows were written by other CTAs in an earlier phase: read through L2 (ld.cg).  D <= 1280.
 template <int R>
-__device__ __forceinline__ void ln_rows(const float *x, const float *w, const float *b, float *xs, int D)
+__device__ __noinline__ void ln_rows(const float *x, const float *w, const float *b, float *xs, float *red, int D)
 {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp < R) {
-        const float4 *xr = reinterpret_cast<const float4 *>(x + (size_t)warp * D);
-        float4 *row = reinterpret_cast<float4 *>(xs + (size_t)warp * D);
-        const int cnt = D >> 2;            // float4 per row (D is a multiple of 64)
-        float s = 0.0f;
-        for (int i = lane; i < cnt; i += 32) {
-            const float4 v = __ldcg(xr + i);
-            row[i] = v;
-            s += (v.x + v.y) + (v.z + v.w);
-        }
-        const float mean = warp_sum_d(s) / (float)D;
-        float qv = 0.0f;
-        for (int i = lane; i < cnt; i += 32) {
-            const float4 v = row[i];
-            const float a0 = v.x - mean, a1 = v.y - mean, a2 = v.z - mean, a3 = v.w - mean;
-            qv += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
-        }
-        const float inv = 1.0f / sqrtf(warp_sum_d(qv) / (float)D + 1e-5f);
-        for (int i = lane; i < cnt; i += 32) {
-            const float4 v = row[i];
-            const float4 ww = reinterpret_cast<const float4 *>(w)[i], bb = reinterpret_cast<const float4 *>(b)[i];
-            float4 o;
-            o.x = (v.x - mean) * inv * ww.x + bb.x;
-            o.y = (v.y - mean) * inv * ww.y + bb.y;
-            o.z = (v.z - mean) * inv * ww.z + bb.z;
-            o.w = (v.w - mean) * inv * ww.w + bb.w;
-            row[i] = o;
+    constexpr int TPR = kDT / R, WPR = TPR / 32, NV = (320 + TPR - 1) / TPR;
+    const int tid = threadIdx.x, m = tid / TPR, t = tid - m * TPR, warp = tid >> 5, lane = tid & 31;
+    const int cnt = D >> 2;
+    const float4 *xr = reinterpret_cast<const float4 *>(x + (size_t)m * D);
+    float4 v[NV], ww[NV], bb[NV];
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NV; j++) {                       // all loads (x through L2, gamma/beta) in flight together
+        const int i = t + j * TPR;
+        const bool ok = i < cnt;
+        v[j] = ok ? __ldcg(xr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        ww[j] = ok ? __ldg(reinterpret_cast<const float4 *>(w) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        bb[j] = ok ? __ldg(reinterpret_cast<const float4 *>(b) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < NV; j++) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+    s = warp_sum_d(s);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    float tot = 0.0f;
+#pragma unroll
+    for (int i = 0; i < WPR; i++) tot += red[m * WPR + i];
+    const float mean = tot / (float)D;
+    float qv = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NV; j++) {
+        const int i = t + j * TPR;
+        if (i < cnt) {
+            v[j].x -= mean; v[j].y -= mean; v[j].z -= mean; v[j].w -= mean;
+            qv += (v[j].x * v[j].x + v[j].y * v[j].y) + (v[j].z * v[j].z + v[j].w * v[j].w);
         }
     }
+    qv = warp_sum_d(qv);
+    if (lane == 0) red[32 + warp] = qv;
     __syncthreads();
+    float vt = 0.0f;
+#pragma unroll
+    for (int i = 0; i < WPR; i++) vt += red[32 + m * WPR + i];
+    const float inv = 1.0f / sqrtf(vt / (float)D + 1e-5f);
+    float4 *row = reinterpret_cast<float4 *>(xs + (size_t)m * D);
+#pragma unroll
+    for (int j = 0; j < NV; j++) {
+        const int i = t + j * TPR;
+        if (i < cnt)
+            row[i] = make_float4(v[j].x * inv * ww[j].x + bb[j].x, v[j].y * inv * ww[j].y + bb[j].y,
+                                 v[j].z * inv * ww[j].z + bb[j].z, v[j].w * inv * ww[j].w + bb[j].w);
+    }
+    __syncthreads();
+}
+
+// L2 prefetch of this CTA's chunk of a weight that a LATER phase will stream (weights do not depend on the
+// activations, so the HBM latency hides behind the current phase and its grid barrier).
+__device__ __noinline__ void prefetch_weight(const DecWeight w, const float *ln_w, const float *ln_b, int D)
+{
+    if (ln_w) {                                          // LayerNorm parameters of the consuming phase (every CTA needs all)
+        const int lines = (D * 4 + 127) >> 7;
+        for (int i = threadIdx.x; i < 2 * lines; i += kDT) {
+            const char *p = i < lines ? reinterpret_cast<const char *>(ln_w) + ((size_t)i << 7)
+                                      : reinterpret_cast<const char *>(ln_b) + ((size_t)(i - lines) << 7);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+        }
+    }
+    if (blockIdx.x * w.rpc >= w.n) return;
+    if (w.bias && threadIdx.x < 2) {
+        const char *p = reinterpret_cast<const char *>(w.bias + (size_t)blockIdx.x * w.rpc) + ((size_t)threadIdx.x << 7);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    }
+    const size_t blocks = (size_t)w.kb * w.rpc;
+    const char *pn = reinterpret_cast<const char *>(w.nib + (size_t)blockIdx.x * blocks);
+    const char *ps = reinterpret_cast<const char *>(w.scl + (size_t)blockIdx.x * blocks);
+    const int ln = (int)((blocks * 16 + 127) >> 7), ls = (int)((blocks * 2 + 127) >> 7);
+    for (int i = threadIdx.x; i < ln + ls; i += kDT) {
+        const char *p = i < ln ? pn + ((size_t)i << 7) : ps + ((size_t)(i - ln) << 7);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    }
 }
 
 // ---- attention over an f16 KV cache, query length 1 (attention.rs:93-125 self, :208-236 cross) ----------
@@ -231,20 +336,49 @@ __device__ __forceinline__ void soft_merge(Soft &a, float m2, float l2, const fl
     a.m = mn;
 }
 
-// Units (clip b, head h, split s) are dealt round-robin to the CTAs.  q: global f32 [B][D] (written in the
-// previous phase); K/V: f16 rows of D (head h at column h*64), row stride ldkv, clip stride bstride.
-// part[((b*H + h)*nsplit + s)*66] = (running max, sum, unnormalised o[64]).
+// The keys of all (clip, head) units form one flattened sequence of units*kv keys that is cut into equal ranges
+// of `per` keys, one per CTA (perfect balance for any batch size); a CTA's range touches at most kMaxSeg
+// consecutive units and it writes one partial per touched unit:
+//   part[(cta*kMaxSeg + seg)*68] = unnormalised o[64], running max, sum.
+// q: global f32 [B][D] (written in the previous phase); K/V: f16 rows of D (head h at column h*64), row stride
+// ldkv, clip stride bstride.
+// Few units (units*2 <= grid, e.g. one clip): every unit is cut into ns aligned splits, one per CTA (one segment,
+// one block-wide merge per CTA); kvp = per*ns is the padded unit length.  Many units: kvp = kv, ranges of `per`
+// keys straddle unit boundaries (<= kMaxSeg segments per CTA) for perfect balance.
+struct AttnPlan { int per, kvp; };
+__device__ __forceinline__ AttnPlan attn_plan(int units, int kv, int grid)
+{
+    AttnPlan p;
+    if (units * 2 <= grid) {
+        int ns = min(grid / units, 8);
+        int per = (kv + ns - 1) / ns;
+        if (per < 16) { per = min(kv, 16); ns = (kv + per - 1) / per; }
+        p.per = per; p.kvp = per * ns;
+    } else {
+        const int mn = max((kv + 7) / 8, min(kv, 16));
+        const int per = (int)(((long long)units * kv + grid - 1) / grid);
+        p.per = per < mn ? mn : per; p.kvp = kv;
+    }
+    return p;
+}
+
 template <bool kFreshKV>
-__device__ __forceinline__ void attn_phase(const float *q, int D, const __half *kc, const __half *vc, long long ldkv,
-                                           long long bstride, int kv_len, int B, int H, int nsplit, float *part, float *sm)
+__device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc, const __half *vc, long long ldkv,
+                                        long long bstride, int kv_len, int B, int H, AttnPlan pl, float *part, float *sm)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 3, dch = lane & 7;
-    const int units = B * H * nsplit;
-    const int per = (kv_len + nsplit - 1) / nsplit;
-    for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        const int s = u % nsplit, h = (u / nsplit) % H, b = u / (nsplit * H);
-        const int k0 = s * per, k1 = min(kv_len, k0 + per);
+    const int per = pl.per, kvp = pl.kvp;
+    const int total = B * H * kvp;
+    int start = (int)blockIdx.x * per;
+    const int end = min(total, start + per);
+    for (int seg = 0; start < end && seg < kMaxSeg; seg++) {
+        const int u = start / kvp;
+        const int k0 = start - u * kvp;
+        const int k1p = min(kvp, k0 + (end - start));
+        start += k1p - k0;
+        const int k1 = min(k1p, kv_len);                   // keys beyond kv_len are padding of the aligned plan
+        const int h = u % H, b = u / H;
         float qv[8];
         {
             const float *qp = q + (size_t)b * D + h * 64 + dch * 8;
@@ -260,13 +394,13 @@ __device__ __forceinline__ void attn_phase(const float *q, int D, const __half *
         st.m = -INFINITY; st.l = 0.0f;
 #pragma unroll
         for (int j = 0; j < 8; j++) st.o[j] = 0.0f;
-        for (int base0 = k0 + warp * 4; base0 < k1; base0 += 128) {   // warp-uniform trip count (shuffles inside)
+        for (int base0 = k0 + warp * 4; base0 < k1; base0 += 256) {   // warp-uniform trip count (shuffles inside)
             const int key0 = base0 + g;
-            // two keys per lane group in flight
-            uint4 kq[2], vq[2];
-            bool ok[2];
+            constexpr int NT = 4;                                      // four keys per lane group in flight
+            uint4 kq[NT], vq[NT];
+            bool ok[NT];
 #pragma unroll
-            for (int t = 0; t < 2; t++) {
+            for (int t = 0; t < NT; t++) {
                 const int key = key0 + t * 64;
                 ok[t] = key < k1;
                 if (ok[t]) {
@@ -276,7 +410,7 @@ __device__ __forceinline__ void attn_phase(const float *q, int D, const __half *
                 }
             }
 #pragma unroll
-            for (int t = 0; t < 2; t++) {
+            for (int t = 0; t < NT; t++) {
                 float sc = 0.0f;
                 if (ok[t]) {
                     const __half2 *hp = reinterpret_cast<const __half2 *>(&kq[t]);
@@ -318,50 +452,132 @@ __device__ __forceinline__ void attn_phase(const float *q, int D, const __half *
         }
         if (g == 0) {
             float *dst = sm + warp * kPartStride;
-            if (dch == 0) { dst[0] = st.m; dst[1] = st.l; }
+            if (dch == 0) { dst[64] = st.m; dst[65] = st.l; }
 #pragma unroll
-            for (int j = 0; j < 8; j++) dst[2 + dch * 8 + j] = st.o[j];
+            for (int j = 0; j < 8; j++) dst[dch * 8 + j] = st.o[j];
         }
         __syncthreads();
         if (warp == 0) {
             float M = -INFINITY;
-            for (int w2 = 0; w2 < kDT / 32; w2++) M = fmaxf(M, sm[w2 * kPartStride]);
+            for (int w2 = 0; w2 < kDT / 32; w2++) M = fmaxf(M, sm[w2 * kPartStride + 64]);
             float Lsum = 0.0f, o0 = 0.0f, o1 = 0.0f;
             for (int w2 = 0; w2 < kDT / 32; w2++) {      // fixed order
-                const float mw = sm[w2 * kPartStride];
+                const float mw = sm[w2 * kPartStride + 64];
                 const float sc = (mw == -INFINITY) ? 0.0f : __expf(mw - M);
-                Lsum += sc * sm[w2 * kPartStride + 1];
-                o0 += sc * sm[w2 * kPartStride + 2 + lane];
-                o1 += sc * sm[w2 * kPartStride + 2 + 32 + lane];
+                Lsum += sc * sm[w2 * kPartStride + 65];
+                o0 += sc * sm[w2 * kPartStride + lane];
+                o1 += sc * sm[w2 * kPartStride + 32 + lane];
             }
-            float *pd = part + (size_t)u * kPartStride;
-            if (lane == 0) { pd[0] = M; pd[1] = Lsum; }
-            pd[2 + lane] = o0;
-            pd[2 + 32 + lane] = o1;
+            float *pd = part + (size_t)(blockIdx.x * kMaxSeg + seg) * kPartStride;
+            if (lane == 0) { pd[64] = M; pd[65] = Lsum; }
+            pd[lane] = o0;
+            pd[32 + lane] = o1;
         }
         __syncthreads();
     }
 }
 
-// Merge the key splits of every (clip, head) into the attention output att[R][D] in shared memory.
+// Merge the partials of every (clip, head) into the attention output att[R][D] in shared memory.
+//   stage A: one thread per unit loads its (max, sum) pairs, derives the merge coefficients -> shared memory
+//   stage B: one thread per 4 output columns: coefficient-weighted sum of the partial o vectors (16-byte loads)
 template <int R>
-__device__ __forceinline__ void attn_combine(const float *part, int D, int H, int nsplit, int nrows, float *att)
+__device__ __noinline__ void attn_combine(const float *part, int D, int H, int kv_len, AttnPlan pl, int nrows, float *att,
+                                          float *sc_s /* >= nrows*H*24 floats */)
 {
-    for (int idx = threadIdx.x; idx < R * D; idx += kDT) {
-        const int m = idx / D, col = idx - m * D;
-        if (m >= nrows) { att[idx] = 0.0f; continue; }
-        const int h = col >> 6, d = col & 63;
-        const float *pp = part + (size_t)((m * H + h) * nsplit) * kPartStride;
-        float M = -INFINITY;
-        for (int s = 0; s < nsplit; s++) M = fmaxf(M, __ldcg(pp + s * kPartStride));
-        float num = 0.0f, den = 0.0f;
-        for (int s = 0; s < nsplit; s++) {
-            const float ms = __ldcg(pp + s * kPartStride);
-            const float sc = (ms == -INFINITY) ? 0.0f : __expf(ms - M);
-            den += sc * __ldcg(pp + s * kPartStride + 1);
-            num += sc * __ldcg(pp + s * kPartStride + 2 + d);
+    const int units = nrows * H, per = pl.per, kvp = pl.kvp;
+    if (R <= 2) {
+        // one clip or two: a single pass, every thread fetches the (max, sum, o) of all partials of its 4 columns at
+        // once (one L2 round trip)
+        const int d4 = D >> 2;
+        for (int idx = threadIdx.x; idx < R * d4; idx += kDT) {
+            const int m = idx / d4, c4 = idx - m * d4;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (m < nrows) {
+                const int h = c4 >> 4, dd = (c4 & 15) * 4, u = m * H + h;
+                const int f0 = u * kvp, f1 = f0 + kv_len - 1;     // < 2^31: units * kvp <= 160 * 1500
+                const int c_lo = f0 / per, np = min(f1 / per - c_lo + 1, kMaxParts);
+                float ms[kMaxParts], ls[kMaxParts];
+                float4 v[kMaxParts];
+#pragma unroll
+                for (int p2 = 0; p2 < kMaxParts; p2++) {
+                    const int c = c_lo + p2;
+                    const int pi = c * kMaxSeg + (u - (c * per) / kvp);
+                    const bool ok = p2 < np;
+                    const float *pp = part + (size_t)(ok ? pi : 0) * kPartStride;
+                    ms[p2] = ok ? __ldcg(pp + 64) : -INFINITY;
+                    ls[p2] = ok ? __ldcg(pp + 65) : 0.0f;
+                    v[p2] = ok ? __ldcg(reinterpret_cast<const float4 *>(pp + dd)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                float M = ms[0];
+#pragma unroll
+                for (int p2 = 1; p2 < kMaxParts; p2++) M = fmaxf(M, ms[p2]);
+                float den = 0.0f;
+#pragma unroll
+                for (int p2 = 0; p2 < kMaxParts; p2++) {
+                    const float cfp = (ms[p2] == -INFINITY) ? 0.0f : __expf(ms[p2] - M);
+                    den += cfp * ls[p2];
+                    acc.x += cfp * v[p2].x; acc.y += cfp * v[p2].y; acc.z += cfp * v[p2].z; acc.w += cfp * v[p2].w;
+                }
+                const float inv = 1.0f / den;
+                acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+            }
+            reinterpret_cast<float4 *>(att)[idx] = acc;
         }
-        att[idx] = num / den;
+        __syncthreads();
+        return;
+    }
+    for (int u = threadIdx.x; u < units; u += kDT) {
+        const int f0 = u * kvp, f1 = f0 + kv_len - 1;
+        const int c_lo = f0 / per, c_hi = f1 / per;
+        const int np = min(c_hi - c_lo + 1, kMaxParts);
+        float ms[kMaxParts], ls[kMaxParts];
+        int pi[kMaxParts];
+#pragma unroll
+        for (int p2 = 0; p2 < kMaxParts; p2++) {
+            const int c = c_lo + p2;
+            const int u0 = (c * per) / kvp;                               // first unit of CTA c
+            pi[p2] = c * kMaxSeg + (u - u0);
+            const bool ok = p2 < np;
+            ms[p2] = ok ? __ldcg(part + (size_t)pi[p2] * kPartStride + 64) : -INFINITY;
+            ls[p2] = ok ? __ldcg(part + (size_t)pi[p2] * kPartStride + 65) : 0.0f;
+        }
+        float M = ms[0];
+#pragma unroll
+        for (int p2 = 1; p2 < kMaxParts; p2++) M = fmaxf(M, ms[p2]);
+        float den = 0.0f, cf[kMaxParts];
+#pragma unroll
+        for (int p2 = 0; p2 < kMaxParts; p2++) {
+            cf[p2] = (ms[p2] == -INFINITY) ? 0.0f : __expf(ms[p2] - M);
+            den += cf[p2] * ls[p2];
+        }
+        const float inv = 1.0f / den;
+        float *o = sc_s + u * 24;
+        o[0] = __int_as_float(np);
+#pragma unroll
+        for (int p2 = 0; p2 < kMaxParts; p2++) { o[1 + p2] = cf[p2] * inv; o[12 + p2] = __int_as_float(pi[p2]); }
+    }
+    __syncthreads();
+    const int d4 = D >> 2;
+    for (int idx = threadIdx.x; idx < R * d4; idx += kDT) {
+        const int m = idx / d4, c4 = idx - m * d4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m < nrows) {
+            const int h = c4 >> 4, dd = (c4 & 15) * 4;
+            const float *o = sc_s + (m * H + h) * 24;
+            const int np = __float_as_int(o[0]);
+            float4 v[kMaxParts];
+#pragma unroll
+            for (int p2 = 0; p2 < kMaxParts; p2++)
+                if (p2 < np) v[p2] = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)__float_as_int(o[12 + p2]) * kPartStride + dd));
+#pragma unroll
+            for (int p2 = 0; p2 < kMaxParts; p2++) {
+                if (p2 < np) {
+                    const float cfp = o[1 + p2];
+                    acc.x += cfp * v[p2].x; acc.y += cfp * v[p2].y; acc.z += cfp * v[p2].z; acc.w += cfp * v[p2].w;
+                }
+            }
+        }
+        reinterpret_cast<float4 *>(att)[idx] = acc;
     }
     __syncthreads();
 }
@@ -377,17 +593,10 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
     float *red = xs + (size_t)R * (F > D ? F : D);     // [kDT * R + 1088] partial sums / attention scratch
     const int tid = threadIdx.x;
     unsigned bar_target = 0;
-    int nsplit_self, nsplit_cross;
-    {
-        int ns = (int)gridDim.x / (B * H);
-        if (ns < 1) ns = 1;
-        if (ns > kMaxSplit) ns = kMaxSplit;
-        nsplit_cross = ns;
-        nsplit_self = ns;
-        const int kvl = a.kv_len + 1;
-        if (nsplit_self > (kvl + 63) / 64) nsplit_self = (kvl + 63) / 64;   // at least 64 keys per split
-    }
     const int kv_len = a.kv_len + 1;                   // including the row appended in this step
+    const AttnPlan per_self = attn_plan(B * H, kv_len, (int)gridDim.x);
+    const AttnPlan per_cross = attn_plan(B * H, a.T_enc, (int)gridDim.x);
+    prefetch_weight(a.layers[0].qkv, a.layers[0].ln1w, a.layers[0].ln1b, D);
 
     // ---- phase 0: x[b] = token_embedding[tok[b]] + positional_embedding[pos]  (decoder.rs:317-329)
     for (int b = blockIdx.x; b < B; b += gridDim.x) {
@@ -397,103 +606,95 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
     }
     if (blockIdx.x == 0)
         for (int j = tid; j < (R - B) * D; j += kDT) a.x[(size_t)B * D + j] = 0.0f;   // unused rows of the R-row tile
-    grid_barrier(a.barrier, bar_target, a.dev_err);
+    grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
     for (int l = 0; l < a.n_layers; l++) {
-        const DecLayerW &L = a.layers[l];
+        const DecLayerW &L = a.layers[l];   // kernel-parameter constant bank
         __half *sk = a.self_k + (size_t)l * B * a.ctx * D, *sv = a.self_v + (size_t)l * B * a.ctx * D;
         const __half *ck = a.cross_kv + (size_t)l * B * a.T_enc * 2 * D;
 
         // P1: LN1 -> fused q|k|v projection; q -> a.q, k/v -> f16 cache row kv_len-1 (decoder.rs:84-92, attention.rs:99-113)
-        ln_rows<R>(a.x, L.ln1w, L.ln1b, xs, D);
-        gemv_phase<R>(L.qkv, xs, red, B, [=](int m, int n, float v) {
-            if (n < D) gq[(size_t)m * D + n] = v;
-            else if (n < 2 * D) sk[((size_t)m * ctx + (kv_len - 1)) * D + (n - D)] = __ushort_as_half(f32_to_f16_sat_d(v));
-            else sv[((size_t)m * ctx + (kv_len - 1)) * D + (n - 2 * D)] = __ushort_as_half(f32_to_f16_sat_d(v));
-        });
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        prefetch_weight(L.out, nullptr, nullptr, D);
+        ln_rows<R>(a.x, L.ln1w, L.ln1b, xs, red, D);
+        gemv_phase<R>(L.qkv, xs, red, B, EpiCtx{EPI_QKV, gq, D, sk, sv, ctx, kv_len - 1, D});
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P2: self-attention over the cache (attention.rs:115-119)
-        attn_phase<true>(a.q, D, sk, sv, D, (long long)a.ctx * D, kv_len, B, H, nsplit_self, a.part, red);
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        attn_phase<true>(a.q, D, sk, sv, D, (long long)a.ctx * D, kv_len, B, H, per_self, a.part, red);
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P3: out projection + residual (decoder.rs:91-92)
-        attn_combine<R>(a.part, D, H, nsplit_self, B, xs);
-        gemv_phase<R>(L.out, xs, red, B, [=](int m, int n, float v) {
-            float *p = gx + (size_t)m * D + n;
-            *p = __ldcg(p) + v;
-        });
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        prefetch_weight(L.cq, L.ln2w, L.ln2b, D);
+        attn_combine<R>(a.part, D, H, kv_len, per_self, B, xs, red);
+        gemv_phase<R>(L.out, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D});
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P4: LN2 -> cross-attention query (decoder.rs:95-99, attention.rs:214-217)
-        ln_rows<R>(a.x, L.ln2w, L.ln2b, xs, D);
-        gemv_phase<R>(L.cq, xs, red, B, [=](int m, int n, float v) { gq[(size_t)m * D + n] = v; });
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        prefetch_weight(L.cout, nullptr, nullptr, D);
+        ln_rows<R>(a.x, L.ln2w, L.ln2b, xs, red, D);
+        gemv_phase<R>(L.cq, xs, red, B, EpiCtx{EPI_STORE, gq, D, nullptr, nullptr, 0, 0, D});
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P5: cross-attention over the cached encoder K/V (attention.rs:219-233)
-        attn_phase<false>(a.q, D, ck, ck + D, 2 * D, (long long)a.T_enc * 2 * D, a.T_enc, B, H, nsplit_cross, a.part, red);
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        attn_phase<false>(a.q, D, ck, ck + D, 2 * D, (long long)a.T_enc * 2 * D, a.T_enc, B, H, per_cross, a.part, red);
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P6: cross out projection + residual (decoder.rs:103-104)
-        attn_combine<R>(a.part, D, H, nsplit_cross, B, xs);
-        gemv_phase<R>(L.cout, xs, red, B, [=](int m, int n, float v) {
-            float *p = gx + (size_t)m * D + n;
-            *p = __ldcg(p) + v;
-        });
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        prefetch_weight(L.fc1, L.ln3w, L.ln3b, D);
+        attn_combine<R>(a.part, D, H, a.T_enc, per_cross, B, xs, red);
+        gemv_phase<R>(L.cout, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D});
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P7: LN3 -> fc1 + tanh-GELU (layers.rs:35-41,55-56)
-        ln_rows<R>(a.x, L.ln3w, L.ln3b, xs, D);
-        gemv_phase<R>(L.fc1, xs, red, B, [=](int m, int n, float v) { gh[(size_t)m * F + n] = wq4_gelu_tanh(v); });
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        prefetch_weight(L.fc2, nullptr, nullptr, D);
+        ln_rows<R>(a.x, L.ln3w, L.ln3b, xs, red, D);
+        gemv_phase<R>(L.fc1, xs, red, B, EpiCtx{EPI_GELU, gh, F, nullptr, nullptr, 0, 0, D});
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P8: fc2 + residual (layers.rs:57, decoder.rs:108-110)
+        if (l + 1 < a.n_layers) prefetch_weight(a.layers[l + 1].qkv, a.layers[l + 1].ln1w, a.layers[l + 1].ln1b, D);
+        else prefetch_weight(a.layers[l].fc2, a.lnfw, a.lnfb, D);   // final LayerNorm parameters
         for (int i = tid; i < R * F / 4; i += kDT)
             reinterpret_cast<float4 *>(xs)[i] = __ldcg(reinterpret_cast<const float4 *>(a.h) + i);
         __syncthreads();
-        gemv_phase<R>(L.fc2, xs, red, B, [=](int m, int n, float v) {
-            float *p = gx + (size_t)m * D + n;
-            *p = __ldcg(p) + v;
-        });
-        grid_barrier(a.barrier, bar_target, a.dev_err);
+        gemv_phase<R>(L.fc2, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D});
+        grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
     }
 
-    // ---- final LayerNorm + logits = x . token_embedding^T (decoder.rs:338-343), f16 copy of the matrix
-    ln_rows<R>(a.x, a.lnfw, a.lnfb, xs, D);
+    // ---- final LayerNorm + logits = x . token_embedding^T (decoder.rs:338-343).  The matrix is an f16 copy stored
+    // transposed in 16-byte chunks [D/8][Vp]: lane = vocabulary row, so loads are coalesced, x is a shared-memory
+    // broadcast and no cross-lane reduction is needed.
+    ln_rows<R>(a.x, a.lnfw, a.lnfb, xs, red, D);
     const int warp = tid >> 5, lane = tid & 31;
-    const int V = a.V;
-    const int nwarps = (int)gridDim.x * (kDT / 32);
-    const int rpw = (V + nwarps - 1) / nwarps;
-    const int gw = blockIdx.x * (kDT / 32) + warp;
-    const int v0 = gw * rpw, v1 = min(V, v0 + rpw);
-    const int chunks = D >> 3;                          // 16-byte chunks per row
+    const int V = a.V, Vp = a.Vp;
+    const int chunks = D >> 3;
     const bool pick = a.arg_hi > a.arg_lo && a.next_out != nullptr;
     float best[R];
     int besti[R];
-    int sup[R];
 #pragma unroll
-    for (int m = 0; m < R; m++) { best[m] = -INFINITY; besti[m] = -1; sup[m] = (a.suppress && m < B) ? a.suppress[m] : -1; }
-    for (int v = v0; v < v1; v++) {
-        const uint4 *er = reinterpret_cast<const uint4 *>(a.tok_emb16 + (size_t)v * D);
+    for (int m = 0; m < R; m++) { best[m] = -INFINITY; besti[m] = -1; }
+    const int ngroups = Vp >> 5;                        // groups of 32 vocabulary rows
+    for (int gidx = blockIdx.x * (kDT / 32) + warp; gidx < ngroups; gidx += (int)gridDim.x * (kDT / 32)) {
+        const int v = gidx * 32 + lane;
+        const uint4 *ep = a.tok_emb16t + v;
         float acc[R];
 #pragma unroll
         for (int m = 0; m < R; m++) acc[m] = 0.0f;
-        for (int c0 = lane; c0 < chunks; c0 += 128) {
-            uint4 e[4];
+        for (int c0 = 0; c0 < chunks; c0 += 8) {
+            uint4 e[8];
 #pragma unroll
-            for (int u = 0; u < 4; u++)
-                if (c0 + 32 * u < chunks) e[u] = ldg_stream16(er + c0 + 32 * u);
+            for (int u = 0; u < 8; u++)
+                if (c0 + u < chunks) e[u] = ldg_stream16(ep + (size_t)(c0 + u) * Vp);
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const int c = c0 + 32 * u;
-                if (c < chunks) {
+            for (int u = 0; u < 8; u++) {
+                if (c0 + u < chunks) {
                     const __half2 *hp = reinterpret_cast<const __half2 *>(&e[u]);
                     const float2 f0 = __half22float2(hp[0]), f1 = __half22float2(hp[1]);
                     const float2 f2 = __half22float2(hp[2]), f3 = __half22float2(hp[3]);
 #pragma unroll
                     for (int m = 0; m < R; m++) {
-                        const float4 xa = *reinterpret_cast<const float4 *>(xs + (size_t)m * D + c * 8);
-                        const float4 xb = *reinterpret_cast<const float4 *>(xs + (size_t)m * D + c * 8 + 4);
+                        const float4 xa = *reinterpret_cast<const float4 *>(xs + (size_t)m * D + (c0 + u) * 8);
+                        const float4 xb = *reinterpret_cast<const float4 *>(xs + (size_t)m * D + (c0 + u) * 8 + 4);
                         float s = acc[m];
                         s = fmaf(f0.x, xa.x, s); s = fmaf(f0.y, xa.y, s); s = fmaf(f1.x, xa.z, s); s = fmaf(f1.y, xa.w, s);
                         s = fmaf(f2.x, xb.x, s); s = fmaf(f2.y, xb.y, s); s = fmaf(f3.x, xb.z, s); s = fmaf(f3.y, xb.w, s);
@@ -502,14 +703,26 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
                 }
             }
         }
+        if (v < V) {
 #pragma unroll
-        for (int m = 0; m < R; m++) {
-            const float s = warp_sum_d(acc[m]);
-            if (lane == 0 && m < B) {
-                a.logits[(size_t)m * V + v] = s;
-                // whisper.rs:131-138 max_by: the LAST maximum wins; rows ascend, so ">=" keeps the later one
-                if (pick && v >= a.arg_lo && v < a.arg_hi && v != sup[m] && (besti[m] < 0 || s >= best[m])) { best[m] = s; besti[m] = v; }
+            for (int m = 0; m < R; m++) {
+                if (m < B) {
+                    a.logits[(size_t)m * V + v] = acc[m];
+                    const int sup = a.suppress ? a.suppress[m] : -1;
+                    // whisper.rs:131-138 max_by: the LAST maximum wins; a lane's rows ascend, so ">=" keeps the later one
+                    if (pick && v >= a.arg_lo && v < a.arg_hi && v != sup && (besti[m] < 0 || acc[m] >= best[m])) { best[m] = acc[m]; besti[m] = v; }
+                }
             }
+        }
+    }
+    // warp-level merge of the 32 lanes' candidates (higher index wins ties)
+#pragma unroll
+    for (int m = 0; m < R; m++) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best[m], off);
+            const int oi = __shfl_xor_sync(0xffffffffu, besti[m], off);
+            if (oi >= 0 && (besti[m] < 0 || ov > best[m] || (ov == best[m] && oi > besti[m]))) { best[m] = ov; besti[m] = oi; }
         }
     }
     if (!pick) return;                                  // uniform over the grid
@@ -524,18 +737,18 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
         float bv = -INFINITY; int bi = -1;
         for (int w2 = 0; w2 < kDT / 32; w2++) {
             const float v = red[(w2 * R + tid) * 2]; const int i = __float_as_int(red[(w2 * R + tid) * 2 + 1]);
-            if (i >= 0 && (bi < 0 || v >= bv)) { bv = v; bi = i; }
+            if (i >= 0 && (bi < 0 || v > bv || (v == bv && i > bi))) { bv = v; bi = i; }
         }
         a.arg_scratch[((size_t)blockIdx.x * kMaxR + tid) * 2] = bv;
         a.arg_scratch[((size_t)blockIdx.x * kMaxR + tid) * 2 + 1] = __int_as_float(bi);
     }
-    grid_barrier(a.barrier, bar_target, a.dev_err);
+    grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
     if (blockIdx.x == 0 && tid < B) {
         float bv = -INFINITY; int bi = -1;
         for (int c = 0; c < (int)gridDim.x; c++) {
             const float v = __ldcg(a.arg_scratch + ((size_t)c * kMaxR + tid) * 2);
             const int i = __float_as_int(__ldcg(a.arg_scratch + ((size_t)c * kMaxR + tid) * 2 + 1));
-            if (i >= 0 && (bi < 0 || v >= bv)) { bv = v; bi = i; }
+            if (i >= 0 && (bi < 0 || v > bv || (v == bv && i > bi))) { bv = v; bi = i; }
         }
         a.next_out[tid] = bi;
     }
@@ -562,10 +775,22 @@ __global__ void decw_build_kernel(const uint4 *__restrict__ pnib, const __half *
     }
 }
 
-__global__ void cvt_f32_f16_kernel(const float *__restrict__ src, __half *__restrict__ dst, long long n)
+// f32 [V][D] -> f16 16-byte chunks [D/8][Vp]; rows >= V are zero
+__global__ void logits_matrix_kernel(const float *__restrict__ emb, uint4 *__restrict__ dst, int V, int Vp, int D)
 {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        dst[i] = __ushort_as_half(f32_to_f16_sat_d(src[i]));
+    const long long total = (long long)(D >> 3) * Vp;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int v = (int)(i % Vp), c = (int)(i / Vp);
+        uint4 o = make_uint4(0, 0, 0, 0);
+        if (v < V) {
+            const float *src = emb + (size_t)v * D + c * 8;
+            uint32_t h[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) h[j] = f32_to_f16_sat_d(src[j]);
+            o = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
+        }
+        dst[i] = o;
+    }
 }
 
 template <int R>
@@ -599,6 +824,11 @@ int32_t launch_decode(const DecodeStepArgs &a, int device, cudaStream_t st)
 
 int wq4m_decode_grid(int device) { return wq4_sm_count(device); }
 
+// Debug hook (not part of the drop-in surface): dev_ptr = kDecTimelineSlots x int64 receiving CTA 0's globaltimer (ns)
+// after every grid barrier of the following decode steps; NULL disables.
+static long long *g_dec_timeline_host = nullptr;
+extern "C" WQ4_API void wq4_debug_decode_timeline(void *dev_ptr) { g_dec_timeline_host = reinterpret_cast<long long *>(dev_ptr); }
+
 int32_t wq4m_decw_create(const wq4_tensor *t, const float *bias_dev, int n_cta, DecWeight *out, void **alloc_nib, void **alloc_scl,
                          cudaStream_t st)
 {
@@ -620,16 +850,18 @@ int32_t wq4m_decw_create(const wq4_tensor *t, const float *bias_dev, int n_cta, 
     return WQ4_OK;
 }
 
-int32_t wq4m_cvt_f32_f16(const float *src, void *dst, int64_t n, cudaStream_t st)
+int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, int64_t D, cudaStream_t st)
 {
-    cvt_f32_f16_kernel<<<2048, 256, 0, st>>>(src, reinterpret_cast<__half *>(dst), (long long)n);
+    logits_matrix_kernel<<<4096, 256, 0, st>>>(emb, reinterpret_cast<uint4 *>(dst), (int)V, (int)Vp, (int)D);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;
 }
 
-int32_t wq4m_decode_step(const DecodeStepArgs &a, int device, cudaStream_t st)
+int32_t wq4m_decode_step(const DecodeStepArgs &a_in, int device, cudaStream_t st)
 {
+    DecodeStepArgs a = a_in;
+    a.timeline = g_dec_timeline_host;
     if (a.B < 1 || a.B > kMaxR) { wq4_set_error("decode step kernel handles 1..8 clips, got %d", a.B); return WQ4_ERR_INVALID; }
     if (a.D % 64 != 0 || a.D > 1280 || a.D != a.H * 64) { wq4_set_error("decode step kernel: unsupported d_model %d / heads %d", a.D, a.H); return WQ4_ERR_UNSUPPORTED; }
     WqProfScope prof(WQ4_PROF_GEMV, 0.0, st);

@@ -36,12 +36,15 @@ struct DecLayerW {
     const float *ln1w, *ln1b, *ln2w, *ln2b, *ln3w, *ln3b;
     DecWeight qkv, out, cq, cout, fc1, fc2;
 };
-struct DecodeStepArgs {
-    const DecLayerW *layers;      // device array [n_layers]
+constexpr int kDecMaxLayers = 32;
+constexpr int kDecTimelineSlots = 512;
+struct DecodeStepArgs {           // passed BY VALUE: the per-layer table sits in the kernel-parameter constant bank
+    DecLayerW layers[kDecMaxLayers];
     int n_layers, B, D, F, H, V, ctx, T_enc;
     const int *tokens;            // [B] device
     const float *tok_emb;         // [V][D] f32 (embedding lookup)
-    const __half *tok_emb16;      // [V][D] f16 (logits matrix)
+    const uint4 *tok_emb16t;      // logits matrix, f16, transposed in 16-byte chunks: [D/8][Vp] (Vp = V rounded up to 32)
+    int Vp;
     const float *pos_emb;         // [ctx][D]
     int emb_pos;                  // positional row of this step
     int kv_len;                   // self-attention cache rows valid BEFORE this step (the new row is written at kv_len)
@@ -56,10 +59,12 @@ struct DecodeStepArgs {
     float *arg_scratch;           // [grid][B][2]
     unsigned *barrier;            // grid barrier counter (zeroed before every launch)
     int *dev_err;
+    long long *timeline;   // debug: kDecTimelineSlots x int64 barrier time stamps, normally NULL
 };
 // Builds the decode layout of a panel-layout tensor (device to device).
 int32_t wq4m_decw_create(const wq4_tensor *t, const float *bias_dev, int n_cta, DecWeight *out, void **alloc_nib, void **alloc_scl,
                          cudaStream_t st);
 int wq4m_decode_grid(int device);
 int32_t wq4m_decode_step(const DecodeStepArgs &a, int device, cudaStream_t st);
-int32_t wq4m_cvt_f32_f16(const float *src, void *dst, int64_t n, cudaStream_t st);
+// f32 [V][D] -> f16 chunks [D/8][Vp] (rows >= V zero)
+int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, int64_t D, cudaStream_t st);

@@ -159,8 +159,8 @@ struct wq4_whisper {
     int64_t max_q = 8;               // rows per batch item in one decoder call (prompt <= 4 tokens)
     // decode-step megakernel state (wq4_decode.cu): decode-layout copies of the decoder linears, f16 logits matrix
     std::vector<DecLayerW> dec_w_host;
-    DecLayerW *dec_w_dev = nullptr;
-    __half *tok_emb16 = nullptr;
+    uint4 *tok_emb16t = nullptr;     // [D/8][Vp] f16 chunks
+    int64_t Vp = 0;
     float *att_part = nullptr, *arg_scratch = nullptr;
     unsigned *grid_bar = nullptr;
     bool decode_kernel_ready = false;
@@ -386,11 +386,10 @@ int32_t reserve(wq4_whisper *m, int64_t B)
             CHK(mk(L.qkv, &W.qkv)); CHK(mk(L.out, &W.out)); CHK(mk(L.cq, &W.cq)); CHK(mk(L.cout, &W.cout));
             CHK(mk(L.fc1, &W.fc1)); CHK(mk(L.fc2, &W.fc2));
         }
-        CHK(dev_alloc(m, &m->dec_w_dev, m->dec.size()));
-        WQ4_CUDA(cudaMemcpy(m->dec_w_dev, m->dec_w_host.data(), m->dec.size() * sizeof(DecLayerW), cudaMemcpyHostToDevice));
-        CHK(dev_alloc(m, &m->tok_emb16, (size_t)m->V * D));
-        CHK(wq4m_cvt_f32_f16(m->tok_emb, m->tok_emb16, m->V * D, nullptr));
-        CHK(dev_alloc(m, &m->att_part, (size_t)8 * m->cfg.n_text_head * 8 * 66));
+        m->Vp = (m->V + 31) / 32 * 32;
+        CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
+        CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
+        CHK(dev_alloc(m, &m->att_part, (size_t)n_cta * 4 * 68));   // [cta][kMaxSeg][68]
         CHK(dev_alloc(m, &m->arg_scratch, (size_t)n_cta * 8 * 2));
         CHK(dev_alloc(m, &m->grid_bar, 4));
         WQ4_CUDA(cudaDeviceSynchronize());
@@ -471,10 +470,12 @@ static bool use_decode_kernel()
 // One decode step for B <= 8 clips as a single persistent kernel (wq4_decode.cu).
 int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
 {
+    if (m->dec.size() > (size_t)kDecMaxLayers) { wq4_set_error("decode step kernel: more than %d decoder layers", kDecMaxLayers); return WQ4_ERR_UNSUPPORTED; }
     DecodeStepArgs a = {};
-    a.layers = m->dec_w_dev; a.n_layers = (int)m->dec.size(); a.B = (int)B; a.D = (int)m->D; a.F = (int)m->F;
+    for (size_t l = 0; l < m->dec.size(); l++) a.layers[l] = m->dec_w_host[l];
+    a.n_layers = (int)m->dec.size(); a.B = (int)B; a.D = (int)m->D; a.F = (int)m->F;
     a.H = m->cfg.n_text_head; a.V = (int)m->V; a.ctx = m->cfg.n_text_ctx; a.T_enc = (int)m->T_enc;
-    a.tokens = m->d_tokens; a.tok_emb = m->tok_emb; a.tok_emb16 = m->tok_emb16; a.pos_emb = m->dec_pos;
+    a.tokens = m->d_tokens; a.tok_emb = m->tok_emb; a.tok_emb16t = m->tok_emb16t; a.Vp = (int)m->Vp; a.pos_emb = m->dec_pos;
     a.emb_pos = (int)emb_pos; a.kv_len = (int)kv_pos0;
     a.x = m->dx; a.q = m->dq; a.h = m->dh; a.part = m->att_part;
     a.self_k = m->self_k; a.self_v = m->self_v; a.cross_kv = m->cross_kv;
@@ -488,7 +489,7 @@ int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv
 
 int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
 {
-    if (q_len == 1 && B <= 8 && m->decode_kernel_ready && use_decode_kernel()) {
+    if (q_len == 1 && B <= 8 && m->decode_kernel_ready && use_decode_kernel() && m->dec.size() <= (size_t)kDecMaxLayers) {
         if (kv_pos0 + 1 > m->cfg.n_text_ctx || emb_pos0 + 1 > m->cfg.n_text_ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
         return decode_step_fused(m, B, emb_pos0, kv_pos0, arg, st);
     }
