@@ -50,16 +50,24 @@ def graph_time(fn_of_i, reps, iters=5):
     return best
 
 
-def bench_gemm(rows, n, k, flags=0, reps=20):
+def bench_gemm(rows, n, k, flags=0, reps=20, mode="f32"):
+    """mode: f32 (q4_matmul drop-in), f16 (bias -> f16, fused QKV), gelu (bias+GELU -> f16, fc1), res (bias + residual
+    -> f32 in place, out-proj / fc2): the four epilogues the encoder uses."""
     copies = max(2, min(reps, int(300e6 // (n * k * 0.5625)) + 1))
     ws = make_weights(n, k, copies)
     x16 = torch.randn((rows, k), device=DEV, dtype=torch.float16)
-    y = torch.empty((rows, n), device=DEV, dtype=torch.float32)
+    y = torch.zeros((rows, n), device=DEV, dtype=torch.float32)
+    y16 = torch.empty((rows, n), device=DEV, dtype=torch.float16)
+    bias = torch.randn(n, device=DEV)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    if mode == "gelu":
+        flags |= wb.WQ4_EPI_GELU
 
     def run(i):
         w = ws[i % copies]
-        wb._lib.check(L.wq4_linear_forward_ex(w._h, None, None, C.c_void_p(x16.data_ptr()), C.c_void_p(y.data_ptr()),
-                                              None, None, rows, flags | wb.WQ4_FORCE_GEMM, None, 0,
+        b_, y32_, y16_, res_ = {"f32": (None, p(y), None, None), "f16": (p(bias), None, p(y16), None),
+                                "gelu": (p(bias), None, p(y16), None), "res": (p(bias), p(y), None, p(y))}[mode]
+        wb._lib.check(L.wq4_linear_forward_ex(w._h, b_, None, p(x16), y32_, y16_, res_, rows, flags | wb.WQ4_FORCE_GEMM, None, 0,
                                               C.c_void_p(_stream(DEV))))
     dt = graph_time(run, reps)
     tile = C.c_int32()
@@ -87,12 +95,13 @@ if __name__ == "__main__":
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--rows", default="", help="comma-separated GEMM row counts (default 1500,6000,48000)")
     ap.add_argument("--no-gemv", action="store_true")
+    ap.add_argument("--mode", default="f32", choices=["f32", "f16", "gelu", "res"])
     a = ap.parse_args()
     shapes = [(1280, 1280), (5120, 1280), (1280, 5120), (3840, 1280), (1024, 1024), (4096, 1024), (1024, 4096)]
     print("-- GEMM, f16 activations resident, CUDA-graph replay, weights rotate through >L2 --")
     for rows in (tuple(int(r) for r in a.rows.split(',')) if a.rows else (1500,) if a.quick else (1500, 6000, 48000)):
         for n, k in shapes:
-            dt, tile = bench_gemm(rows, n, k, reps=20 if rows < 20000 else 6)
+            dt, tile = bench_gemm(rows, n, k, reps=20 if rows < 20000 else 6, mode=a.mode)
             print(f"rows {rows:6d} N {n:5d} K {k:5d} tile_m {tile:3d}: {dt*1e6:9.1f} us {2*rows*n*k/dt/1e12:8.1f} TFLOP/s "
                   f"({2*rows*n*k/dt/1e12/1679*100:5.1f}% of measured 1679)", flush=True)
     print("-- GEMV, f32, CUDA-graph replay --")

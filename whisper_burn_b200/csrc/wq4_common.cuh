@@ -151,11 +151,14 @@ int32_t wq4_launch_cvt_f32_to_16(const float *src, void *dst, int64_t n_elems, b
 __device__ __forceinline__ float wq4_gelu_tanh(float h)
 {
     // src/model/layers.rs:35-41: 0.5*h*(1 + tanh(u)), u = sqrt(2/pi)*(h + 0.044715 h^3).
-    // 0.5*(1 + tanh(u)) == 1/(1 + exp(-2u)); evaluated with ex2/rcp (rel. error ~1e-6).
-    const float c = 0.7978845608028654f;
-    float u = c * (h + 0.044715f * h * h * h);
-    float e = __expf(-2.0f * u);
-    return __fdividef(h, 1.0f + e);
+    // 0.5*(1 + tanh(u)) == 1/(1 + exp(-2u)) == 1/(1 + 2^(h*(k0 + k1*h^2))), k0 = -2*log2(e)*sqrt(2/pi):
+    // 3 FMA-pipe ops + ex2 + add + rcp + mul, relative error ~1e-6, exact limits (0 for h -> -inf, h for h -> +inf).
+    const float k0 = -2.3022081985f, k1 = k0 * 0.044715f;
+    const float a = h * fmaf(h * h, k1, k0);
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+    return h * r;
 }
 
 // Undo the nibble interleave of one 32-bit word: returns the 8 element nibbles e0..e7

@@ -26,7 +26,8 @@
 //   warp 3      TMEM allocator (cta_group::2, 512 columns)
 //   warps 4-11  dequantisers  two sets of four warps alternate over K stages; thread r of a set owns weight
 //                             row r: 2 blocks -> 32 x half2 -> one tcgen05.st.32x32b.x32
-//   warps 12-15 epilogue      tcgen05.ld -> +bias -> GELU -> +residual -> f32 / f16 stores
+//   warps 12-15 epilogue      tcgen05.ld -> +bias -> GELU -> +residual -> f32 / f16 stores; two accumulator buffers
+//                             (TILE_M <= 192) so it runs under the next tile's MMAs
 // Barriers: "full"-type barriers (x_full, a_full, acc_empty) live in the leader CTA and are arrived on by
 // both CTAs (remote arrive / TMA complete_tx on a mapa address); "empty"-type barriers (x_empty, a_empty,
 // acc_full) live in each CTA and are signalled by the leader's tcgen05.commit multicast.
@@ -58,9 +59,12 @@ struct Cfg2 {
     static constexpr int HM = TILE_M / 2;                 // activation rows this CTA keeps
     static constexpr int x_box = HM * 64 * 2;             // bytes of one 64-wide TMA box
     static constexpr int x_stage = 2 * x_box;
-    static constexpr int ACC = TILE_M >= 192 ? 1 : 2;     // accumulator buffers in TMEM
+    static constexpr int ACC = TILE_M >= 256 ? 1 : 2;     // accumulator buffers in TMEM (2: epilogue overlaps the next tile)
     static constexpr int a_col0 = ACC * TILE_M;           // first TMEM column of the A ring
-    static_assert(a_col0 + kStages2 * kAColsPerStage <= 512, "TMEM budget");
+    // A-ring depth: what the 512 columns leave after the accumulators (192 rows: 2 slots; the dequantisers hold the
+    // next stage in registers while they wait for a slot, so two slots already keep the tensor pipe fed)
+    static constexpr int AST = (512 - a_col0) / kAColsPerStage < kStages2 ? (512 - a_col0) / kAColsPerStage : kStages2;
+    static_assert(AST >= 2 && a_col0 + AST * kAColsPerStage <= 512, "TMEM budget");
     static constexpr int x_off = 0;
     static constexpr int raw_off = x_off + kStages2 * x_stage;
     static constexpr int bar_off = raw_off + kRawStages2 * kRawStage;
@@ -150,28 +154,36 @@ __device__ __forceinline__ uint32_t scale_pair(uint16_t sb)
     }
 }
 
-// Epilogue of one 32-column chunk: lane = output column n, v[j] = accumulator of activation row tb + j.
-template <bool GELU, bool RES, bool Y32, bool Y16, bool kBF16>
-__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], float bias, int nvalid, float *y32, void *y16,
-                                          const float *res, long long ld)
+// Epilogue of one 32-column chunk: lane = output column n, v[j] = accumulator of activation row tb + j,
+// r[j] = residual value (RES only, loaded by the caller one chunk ahead).  All 32 values are computed
+// unconditionally so the 32 chains overlap (guarding each element serialises bias/GELU behind a branch);
+// only the stores of a ragged last chunk are predicated.
+template <bool GELU, bool RES, bool Y32, bool Y16, bool kBF16, typename Prefetch>
+__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], float (&r)[32], float bias, int nvalid,
+                                          float *y32, void *y16, long long ld, Prefetch &&prefetch_next)
 {
-    float r[32];
-    if constexpr (RES) {
-#pragma unroll
-        for (int j = 0; j < 32; j++) r[j] = (j < nvalid) ? res[(long long)j * ld] : 0.0f;
-    }
+    float val[32];
 #pragma unroll
     for (int j = 0; j < 32; j++) {
-        float val = __uint_as_float(v[j]) + bias;
-        if constexpr (GELU) val = wq4_gelu_tanh(val);
-        if constexpr (RES) val += r[j];
-        if (j < nvalid) {
-            if constexpr (Y32) y32[(long long)j * ld] = val;
-            if constexpr (Y16) {
-                if constexpr (kBF16) reinterpret_cast<__nv_bfloat16 *>(y16)[(long long)j * ld] = __float2bfloat16_rn(val);
-                else reinterpret_cast<__half *>(y16)[(long long)j * ld] = __float2half_rn(val);
-            }
+        val[j] = __uint_as_float(v[j]) + bias;
+        if constexpr (GELU) val[j] = wq4_gelu_tanh(val[j]);
+        if constexpr (RES) val[j] += r[j];
+    }
+    if constexpr (RES) prefetch_next();       // r[] is free again: next chunk's residual loads fly under the stores
+    auto store = [&](int j) {
+        if constexpr (Y32) y32[(long long)j * ld] = val[j];
+        if constexpr (Y16) {
+            if constexpr (kBF16) reinterpret_cast<__nv_bfloat16 *>(y16)[(long long)j * ld] = __float2bfloat16_rn(val[j]);
+            else reinterpret_cast<__half *>(y16)[(long long)j * ld] = __float2half_rn(val[j]);
         }
+    };
+    if (nvalid == 32) {
+#pragma unroll
+        for (int j = 0; j < 32; j++) store(j);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; j++)
+            if (j < nvalid) store(j);
     }
 }
 
@@ -258,7 +270,7 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
                     tc_fence_after();
                     const uint64_t bdesc0 = umma_smem_desc_sw128(x_smem + s * L::x_stage);
                     const uint64_t bdesc1 = umma_smem_desc_sw128(x_smem + s * L::x_stage + L::x_box);
-                    const uint32_t a_tmem = tmem_base + L::a_col0 + s * kAColsPerStage;
+                    const uint32_t a_tmem = tmem_base + L::a_col0 + (c % L::AST) * kAColsPerStage;
                     if (elect_one()) {
 #pragma unroll
                         for (int k = 0; k < 4; k++)
@@ -325,9 +337,12 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
             __syncwarp();                             // every lane has consumed its raw bytes
             if (elect_one()) mbar_arrive(bar_raw_empty(rs));
             const int s = c % S;
-            mbar_wait(bar_empty(s), ((c / S) & 1u) ^ 1u, cta_abort, p.dev_err, 207);
+            if (c >= (uint32_t)L::AST) {              // slot c % AST is free once the MMA of stage c - AST has completed
+                const uint32_t pc = c - L::AST;
+                mbar_wait(bar_empty(pc % S), (pc / S) & 1u, cta_abort, p.dev_err, 207);
+            }
             tc_fence_after();
-            tmem_st_32x32b_x32(my_tmem + s * kAColsPerStage, v);
+            tmem_st_32x32b_x32(my_tmem + (c % L::AST) * kAColsPerStage, v);
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
@@ -349,11 +364,21 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
             const int panel = (tile % p.npairs) * 2 + crank;
             const int t0 = (tile / p.npairs) * TILE_M;
             const uint32_t ab = it % ACC;
-            mbar_wait(bar_acc_full(ab), (it / ACC) & 1u, cta_abort, p.dev_err, 208);
-            tc_fence_after();
             const int n = panel * WQ4_PANEL_ROWS + q * 32 + lane;
             const bool n_ok = n < p.n;
             const float bias = (p.bias && n_ok) ? p.bias[n] : 0.0f;
+            // residual values are fetched one chunk ahead (first chunk: before the accumulator is even ready)
+            float r[32];
+            auto load_res = [&](int c0) {
+                const int tb = t0 + c0;
+                const float *res = p.residual + (long long)tb * p.ldy + n;
+                const int nv = n_ok ? p.rows - tb : 0;
+#pragma unroll
+                for (int j = 0; j < 32; j++) r[j] = (j < nv) ? __ldg(res + (long long)j * p.ldy) : 0.0f;
+            };
+            if (mode == 3) load_res(0);
+            mbar_wait(bar_acc_full(ab), (it / ACC) & 1u, cta_abort, p.dev_err, 208);
+            tc_fence_after();
 #pragma unroll 1
             for (int c0 = 0; c0 < TILE_M; c0 += 32) {
                 const int tb = t0 + c0;
@@ -361,26 +386,26 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
                 uint32_t v[32];
                 tmem_ld_32x32b_x32(tmem_base + ab * TILE_M + c0 + ((uint32_t)(q * 32) << 16), v);
                 tmem_ld_wait();
+                auto prefetch = [&] { if (c0 + 32 < TILE_M && tb + 32 < p.rows) load_res(c0 + 32); };
                 if (!n_ok) continue;
                 const int nvalid = min(32, p.rows - tb);
                 const long long o = (long long)tb * p.ldy + n;
                 float *y32 = p.y32 ? p.y32 + o : nullptr;
-                const float *res = p.residual ? p.residual + o : nullptr;
                 void *y16 = nullptr;
                 if (p.y16) y16 = kBF16 ? (void *)(reinterpret_cast<__nv_bfloat16 *>(p.y16) + o)
                                        : (void *)(reinterpret_cast<__half *>(p.y16) + o);
                 switch (mode) {
-                case 0: epi_chunk<false, false, true, false, kBF16>(v, bias, nvalid, y32, y16, res, p.ldy); break;
-                case 1: epi_chunk<false, false, false, true, kBF16>(v, bias, nvalid, y32, y16, res, p.ldy); break;
-                case 2: epi_chunk<true, false, false, true, kBF16>(v, bias, nvalid, y32, y16, res, p.ldy); break;
-                case 3: epi_chunk<false, true, true, false, kBF16>(v, bias, nvalid, y32, y16, res, p.ldy); break;
+                case 0: epi_chunk<false, false, true, false, kBF16>(v, r, bias, nvalid, y32, y16, p.ldy, prefetch); break;
+                case 1: epi_chunk<false, false, false, true, kBF16>(v, r, bias, nvalid, y32, y16, p.ldy, prefetch); break;
+                case 2: epi_chunk<true, false, false, true, kBF16>(v, r, bias, nvalid, y32, y16, p.ldy, prefetch); break;
+                case 3: epi_chunk<false, true, true, false, kBF16>(v, r, bias, nvalid, y32, y16, p.ldy, prefetch); break;
                 default:
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
+                        float val = __uint_as_float(v[j]) + bias;
+                        if (f_gelu) val = wq4_gelu_tanh(val);
+                        if (f_res) val += __ldg(p.residual + o + (long long)min(j, nvalid - 1) * p.ldy);
                         if (j < nvalid) {
-                            float val = __uint_as_float(v[j]) + bias;
-                            if (f_gelu) val = wq4_gelu_tanh(val);
-                            if (f_res) val += res[(long long)j * p.ldy];
                             if (f_y32) y32[(long long)j * p.ldy] = val;
                             if (f_y16) {
                                 if constexpr (kBF16) reinterpret_cast<__nv_bfloat16 *>(y16)[(long long)j * p.ldy] = __float2bfloat16_rn(val);
@@ -459,7 +484,8 @@ int32_t launch2(const CUtensorMap &tx, const Gemm2Params &p, int device, cudaStr
 }  // namespace
 
 // Row-tile heuristic for the CTA-pair kernel.  Per pair tile the time is ~ max(MMA, dequant) per K stage plus a
-// fixed fill/drain part; cost model in units of "activation rows": waves * (max(tile_m, 96) + 48).
+// fixed fill/drain part; cost model in units of "activation rows": waves * (max(tile_m, 150) + 48), fitted to
+// profiles/r01 (per pair tile at K = 1280: 6.1 / 7.3 / 10.6 us for 128 / 192 / 256 rows).
 int wq4_pick_tile_m2(int64_t rows, int64_t npairs)
 {
     static int forced = -1;
@@ -476,7 +502,7 @@ int wq4_pick_tile_m2(int64_t rows, int64_t npairs)
         const int tm = cands[i];
         const int64_t tiles = npairs * ((rows + tm - 1) / tm);
         const int64_t waves = (tiles + pairs - 1) / pairs;
-        const double per = (tm > 96 ? tm : 96) + 48.0 + (tm == 256 ? 40.0 : 0.0);   // 256: epilogue not overlapped
+        const double per = (tm > 150 ? tm : 150) + 48.0 + (tm == 256 ? 46.0 : 0.0);   // 256: epilogue not overlapped
         const double cost = (double)waves * per;
         if (cost < best_cost) { best_cost = cost; best = tm; }
     }
