@@ -4,6 +4,8 @@
 // separate conversion pass exists.
 #include <float.h>
 
+#include <cstdlib>
+
 #include "wq4_common.cuh"
 #include "wq4_model.cuh"
 
@@ -549,6 +551,9 @@ int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y3
 int32_t wq4m_enc_attention(const void *qkv16, void *out16, int64_t B, int64_t T, int64_t D, int64_t H, cudaStream_t st)
 {
     if (D != H * kHD) { wq4_set_error("attention: head_dim must be 64 (attention.rs:30), got D=%lld H=%lld", (long long)D, (long long)H); return WQ4_ERR_SHAPE; }
+    static int impl = -1;
+    if (impl < 0) { const char *e = getenv("WQ4_ATTN_IMPL"); impl = (e && atoi(e) == 1) ? 1 : 0; }   // 1 = mma.sync kernel below
+    if (impl == 0) return wq4m_enc_attention_tc(qkv16, out16, B, T, D, H, st);
     dim3 grid((unsigned)((T + kBQ - 1) / kBQ), (unsigned)H, (unsigned)B);
     const float scale_log2 = 1.4426950408889634f / 8.0f;   // log2(e) / sqrt(64)
     WqProfScope prof(WQ4_PROF_ATTN_ENC, 4.0 * (double)B * (double)H * (double)T * (double)T * 64.0, st);

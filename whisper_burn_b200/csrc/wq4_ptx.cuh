@@ -313,4 +313,47 @@ __host__ __device__ constexpr uint32_t umma_idesc_f16(int m, int n, bool bf16)
            ((uint32_t)(m >> 4) << 24);
 }
 
+// ---- attention kernel additions ------------------------------------------------------------------------
+// D[tmem] (+)= A[tmem] * B[smem], single CTA: A (128 lanes x K f16, two per 32-bit column) read from tensor memory.
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 16 consecutive 32-bit columns of this thread's TMEM lane <- 16 registers
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&v)[16])
+{
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+// Shared-memory descriptor for an MN-major operand tile: rows of 128 bytes = 64 consecutive f16 along M/N for one
+// K index, 128-byte swizzle, 8-row (8 K indices) groups 1024 bytes apart -- exactly what a TMA box {64, rows}
+// with CU_TENSOR_MAP_SWIZZLE_128B writes.  One UMMA (K = 16) spans two groups; advance the start address by
+// 2048 bytes per K step.  (CUTLASS mma_traits_sm100.hpp, canonical layout B128 Major-MN: ((8,n),(8,k)):((1,LBO),(8,SBO))
+// in 16-byte units; n == 1 here so LBO is unused.)
+__device__ __forceinline__ uint64_t umma_smem_desc_mn_sw128(uint32_t smem_addr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// Instruction descriptor, kind::f16, f16 operands, f32 accumulate, A K-major, B MN-major (bit 16).
+__host__ __device__ constexpr uint32_t umma_idesc_f16_bmn(int m, int n)
+{
+    return (1u << 4) | (1u << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
 }  // namespace ptx
