@@ -18,6 +18,7 @@
 #include <cuda.h>
 #include <cuda_fp16.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "wq4_common.cuh"
@@ -52,6 +53,14 @@ struct AttnParams {
     int *dev_err;
 };
 
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads)
+{
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ float ex2f(float x)
 {
     float y;
@@ -252,6 +261,259 @@ enc_attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnPa
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Second arrangement: one CTA per SM, TWO query tiles (256 rows) per CTA sharing every K/V tile, one softmax
+// warpgroup per query tile, all 512 TMEM columns:
+//   S0 [0,128)  S1 [128,256)  P0 [256,320)  P1 [320,384)  O0 [384,448)  O1 [448,512)
+// P no longer aliases S, so S(j+1) = Q K(j+1)^T is issued the moment a warpgroup has pulled S(j) into registers
+// (the whole 128-column row: one pass, max and exp2 from registers), and O accumulates in TMEM across key tiles
+// (rescaled lazily), so neither MMA's latency nor a per-tile read of O is on the softmax path.
+// Registers: setmaxnreg moves the producer warpgroup's allocation to the two softmax warpgroups (40 / 232).
+constexpr int kA2Threads = 384;
+constexpr int kA2Stages = 3;
+constexpr int kA2SmemQ = 0;                                   // two Q tiles
+constexpr int kA2SmemK = kA2SmemQ + 2 * kTile;
+constexpr int kA2SmemV = kA2SmemK + kA2Stages * kTile;
+constexpr int kA2SmemBar = kA2SmemV + kA2Stages * kTile;
+constexpr int kA2NumBars = 1 + 2 * kA2Stages + 8;             // q, kv_full[], kv_empty[], {s_full,s_free,p_full,o_full}[2]
+constexpr int kA2SmemMisc = kA2SmemBar + kA2NumBars * 8;
+constexpr int kA2SmemAlloc = kA2SmemMisc + 16 + 1024;
+
+__global__ void __launch_bounds__(kA2Threads, 1)
+enc_attention_tc2_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p)
+{
+    extern __shared__ uint8_t smem_raw_att[];
+    const uint32_t base = (smem_u32(smem_raw_att) + 1023u) & ~1023u;
+    uint8_t *base_ptr = smem_raw_att + (base - smem_u32(smem_raw_att));
+    const uint32_t bars = base + kA2SmemBar;
+    const uint32_t bar_q = bars;
+    auto bar_kv_full = [&](int s) { return bars + 8u * (1 + s); };
+    auto bar_kv_empty = [&](int s) { return bars + 8u * (1 + kA2Stages + s); };
+    const uint32_t bar_t0 = bars + 8u * (1 + 2 * kA2Stages);
+    auto bar_s_full = [&](int t) { return bar_t0 + 8u * (4 * t); };
+    auto bar_s_free = [&](int t) { return bar_t0 + 8u * (4 * t + 1); };
+    auto bar_p_full = [&](int t) { return bar_t0 + 8u * (4 * t + 2); };
+    auto bar_o_full = [&](int t) { return bar_t0 + 8u * (4 * t + 3); };
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(base_ptr + kA2SmemMisc);
+    volatile int *cta_abort = reinterpret_cast<volatile int *>(base_ptr + kA2SmemMisc + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * 2 * kBQ, h = blockIdx.y, b = blockIdx.z;
+    const int nkv = (p.T + kBK - 1) / kBK;
+
+    if (threadIdx.x == 0) {
+        *cta_abort = 0;
+        mbar_init(bar_q, 1u);
+        for (int s = 0; s < kA2Stages; s++) { mbar_init(bar_kv_full(s), 1u); mbar_init(bar_kv_empty(s), 1u); }
+        for (int t = 0; t < 2; t++) {
+            mbar_init(bar_s_full(t), 1u);
+            mbar_init(bar_s_free(t), 4u);
+            mbar_init(bar_p_full(t), 4u);
+            mbar_init(bar_o_full(t), 1u);
+        }
+        fence_mbar_init();
+        prefetch_tensormap(&tm_qkv);
+    }
+    if (warp == 1) {
+        tmem_alloc(smem_u32(const_cast<uint32_t *>(tmem_slot)), 512u);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 4) {
+        setmaxnreg_dec<40>();
+        if (warp == 0) {
+            // ================================ TMA producer ================================
+            if (elect_one()) {
+                mbar_arrive_expect_tx(bar_q, 2u * kTile);
+                tma_load_3d(base + kA2SmemQ, &tm_qkv, bar_q, h * kHD, q0, b);
+                tma_load_3d(base + kA2SmemQ + kTile, &tm_qkv, bar_q, h * kHD, q0 + kBQ, b);
+            }
+            __syncwarp();
+            for (int j = 0; j < nkv; j++) {
+                const int s = j % kA2Stages;
+                mbar_wait(bar_kv_empty(s), ((j / kA2Stages) & 1u) ^ 1u, cta_abort, p.dev_err, 411);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(bar_kv_full(s), 2u * kTile);
+                    tma_load_3d(base + kA2SmemK + s * kTile, &tm_qkv, bar_kv_full(s), p.D + h * kHD, j * kBK, b);
+                    tma_load_3d(base + kA2SmemV + s * kTile, &tm_qkv, bar_kv_full(s), 2 * p.D + h * kHD, j * kBK, b);
+                }
+                __syncwarp();
+            }
+        } else if (warp == 1) {
+            // ================================ MMA issuer ==================================
+            constexpr uint32_t idesc_s = umma_idesc_f16(kBQ, kBK, false);
+            constexpr uint32_t idesc_o = umma_idesc_f16_bmn(kBQ, kHD);
+            auto issue_s = [&](int t, int j) {
+                const uint64_t qdesc = umma_smem_desc_sw128(base + kA2SmemQ + t * kTile);
+                const uint64_t kdesc = umma_smem_desc_sw128(base + kA2SmemK + (j % kA2Stages) * kTile);
+                if (elect_one()) {
+#pragma unroll
+                    for (int k = 0; k < kHD / 16; k++)
+                        umma_f16(tmem_base + t * 128u, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
+                    umma_commit(bar_s_full(t));
+                }
+                __syncwarp();
+            };
+            mbar_wait(bar_q, 0u, cta_abort, p.dev_err, 412);
+            mbar_wait(bar_kv_full(0), 0u, cta_abort, p.dev_err, 413);
+            tc_fence_after();
+            issue_s(0, 0);
+            issue_s(1, 0);
+            for (int j = 0; j < nkv; j++) {
+                if (j + 1 < nkv) {
+                    const int sn = (j + 1) % kA2Stages;
+                    mbar_wait(bar_kv_full(sn), ((j + 1) / kA2Stages) & 1u, cta_abort, p.dev_err, 413);
+                    for (int t = 0; t < 2; t++) {
+                        mbar_wait(bar_s_free(t), j & 1u, cta_abort, p.dev_err, 414);   // S(j) is in registers
+                        tc_fence_after();
+                        issue_s(t, j + 1);
+                    }
+                }
+                const int s = j % kA2Stages;
+                const uint64_t vdesc = umma_smem_desc_mn_sw128(base + kA2SmemV + s * kTile);
+                for (int t = 0; t < 2; t++) {
+                    mbar_wait(bar_p_full(t), j & 1u, cta_abort, p.dev_err, 415);
+                    tc_fence_after();
+                    if (elect_one()) {
+#pragma unroll
+                        for (int k = 0; k < kBK / 16; k++)
+                            umma_f16_ts(tmem_base + 384u + t * 64u, tmem_base + 256u + t * 64u + 8u * k, vdesc + 128u * k,
+                                        idesc_o, (j | k) != 0 ? 1u : 0u);
+                        umma_commit(bar_o_full(t));
+                        if (t == 1) umma_commit(bar_kv_empty(s));
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ================================ softmax warpgroups ==========================
+        setmaxnreg_inc<232>();
+        const int t = (warp >> 2) - 1;                         // query tile of this warpgroup
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const uint32_t tm_s = tmem_base + lane_sel + t * 128u;
+        const uint32_t tm_p = tmem_base + lane_sel + 256u + t * 64u;
+        const uint32_t tm_o = tmem_base + lane_sel + 384u + t * 64u;
+        const float c = p.scale_log2;
+        // O_t accumulates in TMEM over all key tiles (TMEM reads are 64 B/clk/SM: re-reading a 32 KB partial product
+        // per tile cost as much as the exponentials).  The exponent offset m_used is only raised -- and O and l rescaled,
+        // a TMEM read-modify-write -- when a row's maximum outgrows it by more than 2^8; until then p <= 256, which f16
+        // holds, and the final o / l is exact for any common offset.
+        float m_used = -INFINITY, l_run = 0.0f;
+        for (int j = 0; j < nkv; j++) {
+            const int kvalid = p.T - j * kBK;
+            uint32_t sreg[kBK];
+            mbar_wait(bar_s_full(t), j & 1u, cta_abort, p.dev_err, 416);
+            tc_fence_after();
+            tmem_ld_32x32b_x64(tm_s, sreg);
+            tmem_ld_32x32b_x64(tm_s + 64, sreg + 64);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (elect_one()) mbar_arrive(bar_s_free(t));
+            if (kvalid < kBK) {
+#pragma unroll
+                for (int i = 0; i < kBK; i++)
+                    if (i >= kvalid) sreg[i] = 0xff800000u;    // -inf: key beyond the sequence
+            }
+            float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < kBK; i += 4) {
+                m0 = fmaxf(m0, __uint_as_float(sreg[i]));
+                m1 = fmaxf(m1, __uint_as_float(sreg[i + 1]));
+                m2 = fmaxf(m2, __uint_as_float(sreg[i + 2]));
+                m3 = fmaxf(m3, __uint_as_float(sreg[i + 3]));
+            }
+            const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+            const bool grow = (mx - m_used) * c > 8.0f;        // always true on the first tile (m_used = -inf)
+            const bool warp_grow = __any_sync(0xffffffffu, grow);
+            if (j > 0) {
+                // PV(j-1) complete: O holds tiles < j and the P region may be overwritten
+                mbar_wait(bar_o_full(t), (j - 1) & 1u, cta_abort, p.dev_err, 417);
+                tc_fence_after();
+            }
+            if (warp_grow) {
+                const float m_new = fmaxf(m_used, mx);
+                const float alpha = ex2f((m_used - m_new) * c);    // 1 for lanes whose offset stays; 0 on the first tile
+                m_used = m_new;
+                l_run *= alpha;
+                if (j > 0) {
+                    uint32_t ov[kHD];
+                    tmem_ld_32x32b_x64(tm_o, ov);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < kHD; i++) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+                    tmem_st_32x32b_x64(tm_o, ov);
+                }
+            }
+            const float mc = m_used * c;
+            uint32_t pk[kBK / 2];
+            float sum0 = 0.0f, sum1 = 0.0f;
+            // The exponential phase is bound by the SFU pipe (128 ex2 + 64 f32->f16x2 packs per row, 16 lanes/clk/SM)
+            // and is as long as the rest of a tile (TMEM read at 64 B/clk/SM, max, P store).  The two warpgroups take
+            // turns in it so the SFU never idles; left alone they fall into lockstep and share it at half speed each.
+            if (t == 0) { if (j > 0) named_bar_sync(2, 256); } else named_bar_sync(1, 256);
+#pragma unroll
+            for (int i = 0; i < kBK / 2; i++) {
+                const float p0 = ex2f(fmaf(__uint_as_float(sreg[2 * i]), c, -mc));
+                const float p1 = ex2f(fmaf(__uint_as_float(sreg[2 * i + 1]), c, -mc));
+                sum0 += p0;
+                sum1 += p1;
+                const __half2 hh = __floats2half2_rn(p0, p1);
+                pk[i] = *reinterpret_cast<const uint32_t *>(&hh);
+            }
+            if (t == 0) named_bar_arrive(1, 256); else if (j + 1 < nkv) named_bar_arrive(2, 256);
+            l_run += sum0 + sum1;
+            tmem_st_32x32b_x64(tm_p, pk);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (elect_one()) mbar_arrive(bar_p_full(t));
+        }
+        float o[kHD];
+        {
+            mbar_wait(bar_o_full(t), (nkv - 1) & 1u, cta_abort, p.dev_err, 418);
+            tc_fence_after();
+            uint32_t ov[kHD];
+            tmem_ld_32x32b_x64(tm_o, ov);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < kHD; i++) o[i] = __uint_as_float(ov[i]);
+        }
+        const int qrow = q0 + t * kBQ + row;
+        if (qrow < p.T) {
+            const float inv = 1.0f / l_run;
+            uint4 *dst = reinterpret_cast<uint4 *>(p.out + ((size_t)b * p.T + qrow) * p.D + h * kHD);
+#pragma unroll
+            for (int i = 0; i < kHD / 8; i++) {
+                uint4 w;
+                __half2 h0 = __floats2half2_rn(o[8 * i] * inv, o[8 * i + 1] * inv);
+                __half2 h1 = __floats2half2_rn(o[8 * i + 2] * inv, o[8 * i + 3] * inv);
+                __half2 h2 = __floats2half2_rn(o[8 * i + 4] * inv, o[8 * i + 5] * inv);
+                __half2 h3 = __floats2half2_rn(o[8 * i + 6] * inv, o[8 * i + 7] * inv);
+                w.x = *reinterpret_cast<uint32_t *>(&h0);
+                w.y = *reinterpret_cast<uint32_t *>(&h1);
+                w.z = *reinterpret_cast<uint32_t *>(&h2);
+                w.w = *reinterpret_cast<uint32_t *>(&h3);
+                dst[i] = w;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512u);
+    }
+}
+
 typedef CUresult (*EncodeTiledFnA)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
@@ -298,8 +560,11 @@ int32_t wq4m_enc_attention_tc(const void *qkv16, void *out16, int64_t B, int64_t
     static bool attr_done[64] = {};
     if (device < 0 || device >= 64 || !attr_done[device]) {
         WQ4_CUDA(cudaFuncSetAttribute(enc_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+        WQ4_CUDA(cudaFuncSetAttribute(enc_attention_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2SmemAlloc));
         if (device >= 0 && device < 64) attr_done[device] = true;
     }
+    static int impl = -1;
+    if (impl < 0) { const char *e = getenv("WQ4_ATTN_IMPL"); impl = (e && atoi(e) == 2) ? 2 : 0; }   // 2 = one query tile per CTA
     AttnParams p = {};
     p.out = reinterpret_cast<__half *>(out16);
     p.T = (int)T;
@@ -307,9 +572,14 @@ int32_t wq4m_enc_attention_tc(const void *qkv16, void *out16, int64_t B, int64_t
     p.scale_log2 = 1.4426950408889634f / 8.0f;   // log2(e) / sqrt(64)
     p.dev_err = wq4_error_flag_ptr(device);
     if (!p.dev_err) return WQ4_ERR_CUDA;
-    dim3 grid((unsigned)((T + kBQ - 1) / kBQ), (unsigned)H, (unsigned)B);
     WqProfScope prof(WQ4_PROF_ATTN_ENC, 4.0 * (double)B * (double)H * (double)T * (double)T * 64.0, st);
-    enc_attention_tc_kernel<<<grid, kAttThreads, kSmemAlloc, st>>>(tm, p);
+    if (impl == 2) {
+        dim3 grid((unsigned)((T + kBQ - 1) / kBQ), (unsigned)H, (unsigned)B);
+        enc_attention_tc_kernel<<<grid, kAttThreads, kSmemAlloc, st>>>(tm, p);
+    } else {
+        dim3 grid((unsigned)((T + 2 * kBQ - 1) / (2 * kBQ)), (unsigned)H, (unsigned)B);
+        enc_attention_tc2_kernel<<<grid, kA2Threads, kA2SmemAlloc, st>>>(tm, p);
+    }
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;
