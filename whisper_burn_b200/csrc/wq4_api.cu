@@ -179,6 +179,13 @@ int32_t wq4_launch_cvt_f32_to_16(const float *src, void *dst, int64_t n, bool bf
 }
 
 // ---- dispatch -----------------------------------------------------------------------------------
+bool wq4_pdl_enabled()
+{
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("WQ4_PDL"); v = (e && atoi(e) == 0) ? 0 : 1; }
+    return v != 0;
+}
+
 int wq4_gemm_impl()
 {
     static int impl = -1;

@@ -322,11 +322,13 @@ enc_attention_tc2_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnP
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    grid_dep_launch();      // PDL: see wq4_gemm2.cu; everything this kernel reads comes through the TMA producer
 
     if (warp < 4) {
         setmaxnreg_dec<40>();
         if (warp == 0) {
             // ================================ TMA producer ================================
+            grid_dep_wait();
             if (elect_one()) {
                 mbar_arrive_expect_tx(bar_q, 2u * kTile);
                 tma_load_3d(base + kA2SmemQ, &tm_qkv, bar_q, h * kHD, q0, b);
@@ -577,8 +579,17 @@ int32_t wq4m_enc_attention_tc(const void *qkv16, void *out16, int64_t B, int64_t
         dim3 grid((unsigned)((T + kBQ - 1) / kBQ), (unsigned)H, (unsigned)B);
         enc_attention_tc_kernel<<<grid, kAttThreads, kSmemAlloc, st>>>(tm, p);
     } else {
-        dim3 grid((unsigned)((T + 2 * kBQ - 1) / (2 * kBQ)), (unsigned)H, (unsigned)B);
-        enc_attention_tc2_kernel<<<grid, kA2Threads, kA2SmemAlloc, st>>>(tm, p);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)((T + 2 * kBQ - 1) / (2 * kBQ)), (unsigned)H, (unsigned)B);
+        cfg.blockDim = dim3(kA2Threads, 1, 1);
+        cfg.dynamicSmemBytes = kA2SmemAlloc;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = wq4_pdl_enabled() ? 1 : 0;
+        WQ4_CUDA(cudaLaunchKernelEx(&cfg, enc_attention_tc2_kernel, tm, p));
     }
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());

@@ -144,6 +144,9 @@ struct DenseGemmArgs {
 };
 int32_t wq4_launch_gemm_dense(const DenseGemmArgs &a, int tile_m);
 
+// PDL on the encoder chain (GEMM, LayerNorm, attention); WQ4_PDL=0 turns the launch attribute off (A/B runs).
+bool wq4_pdl_enabled();
+
 int32_t wq4_launch_cvt_f32_to_16(const float *src, void *dst, int64_t n_elems, bool bf16,
                                  cudaStream_t stream);
 

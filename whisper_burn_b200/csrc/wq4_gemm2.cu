@@ -51,7 +51,7 @@ constexpr int kRawScl = 4 * WQ4_PANEL_ROWS * 2;          // 1 KiB
 constexpr int kRawStage = kRawNib + kRawScl;             // 9216 B
 constexpr int kRawStages2 = 8;
 constexpr int kAColsPerStage = kBK2 / 2;                 // 64 TMEM columns: 128 f16 per lane, two per column
-constexpr int kStages2 = 4;                              // unified ring: X tile in shared memory + A tile in TMEM
+constexpr int kAStagesMax = 4;                           // deepest TMEM weight ring (64 columns per slot)
 
 template <int TILE_M>
 struct Cfg2 {
@@ -63,13 +63,15 @@ struct Cfg2 {
     static constexpr int a_col0 = ACC * TILE_M;           // first TMEM column of the A ring
     // A-ring depth: what the 512 columns leave after the accumulators (192 rows: 2 slots; the dequantisers hold the
     // next stage in registers while they wait for a slot, so two slots already keep the tensor pipe fed)
-    static constexpr int AST = (512 - a_col0) / kAColsPerStage < kStages2 ? (512 - a_col0) / kAColsPerStage : kStages2;
+    static constexpr int AST = (512 - a_col0) / kAColsPerStage < kAStagesMax ? (512 - a_col0) / kAColsPerStage : kAStagesMax;
+    // X ring in shared memory (decoupled from the TMEM weight ring; depth beyond 4 measured neutral)
+    static constexpr int S = TILE_M == 192 ? 6 : 4;
     static_assert(AST >= 2 && a_col0 + AST * kAColsPerStage <= 512, "TMEM budget");
     static constexpr int x_off = 0;
-    static constexpr int raw_off = x_off + kStages2 * x_stage;
+    static constexpr int raw_off = x_off + S * x_stage;
     static constexpr int bar_off = raw_off + kRawStages2 * kRawStage;
     // full[S] empty[S] raw_full[R] raw_empty[R] acc_full[ACC] acc_empty[ACC]
-    static constexpr int n_bars = 2 * kStages2 + 2 * kRawStages2 + 2 * ACC;
+    static constexpr int n_bars = 2 * S + 2 * kRawStages2 + 2 * ACC;
     static constexpr int misc_off = bar_off + n_bars * 8;
     static constexpr int total = misc_off + 16;
     static constexpr int alloc = total + 1024;
@@ -92,6 +94,7 @@ struct Gemm2Params {
     long long ldy;  // output row stride (elements)
     uint32_t flags;
     int *dev_err;
+    long long *timeline;   // debug (wq4_debug_gemm_timeline): clock64 stamps of CTA 0's roles, normally NULL
 };
 
 __device__ __forceinline__ uint32_t lop3_and_or2(uint32_t a, uint32_t b, uint32_t c)
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(kThreads2, 1)
 q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
 {
     using L = Cfg2<TILE_M>;
-    constexpr int S = kStages2, RS = kRawStages2, ACC = L::ACC;
+    constexpr int S = L::S, RS = kRawStages2, ACC = L::ACC;
     extern __shared__ uint8_t smem_raw2[];
     const uint32_t base = (smem_u32(smem_raw2) + 1023u) & ~1023u;
     uint8_t *base_ptr = smem_raw2 + (base - smem_u32(smem_raw2));
@@ -233,11 +236,22 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
     cluster_sync_all();     // both CTAs' barriers exist before anything remote can land
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
+#ifdef WQ4_GEMM_TIMELINE      // build.sh -DWQ4_GEMM_TIMELINE: clock64 stamps of CTA 0's role loops (scripts/gemm_timeline.py)
+    long long *const tl = blockIdx.x == 0 ? p.timeline : nullptr;
+#define WQ4_TL(role, c, k) do { if (tl && (c) < 64u && lane == 0) tl[((role) * 64 + (c)) * 4 + (k)] = clock64(); } while (0)
+#else
+#define WQ4_TL(role, c, k) do { } while (0)
+#endif
+    // PDL: the next kernel in the stream may be scheduled from here on (it parks in its own grid_dep_wait()).  In this
+    // kernel only the warps that touch the predecessor's output wait for it -- the X producer and the epilogue; the
+    // weight stream (raw producer, dequantisers -> TMEM) starts under the predecessor's tail.
+    grid_dep_launch();
 
     // Every role loop below is executed by all 32 lanes of its warp (warp-uniform control flow and operands);
     // only the issuing instruction is predicated on an elected lane.
     if (warp == 0) {
         // ================================ X producer (both CTAs) ================================
+        grid_dep_wait();
         const uint32_t full_leader0 = mapa_u32(bar_full(0), 0u);
         uint32_t c = 0;
         for (int tile = slot; tile < num_tiles; tile += nslots) {
@@ -245,6 +259,7 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
             for (int ks = 0; ks < p.kst; ks++, c++) {
                 const int s = c % S;
                 mbar_wait(bar_empty(s), ((c / S) & 1u) ^ 1u, cta_abort, p.dev_err, 201);
+                WQ4_TL(0, c, 0);
                 if (elect_one()) {
                     if (crank == 0) mbar_arrive_expect_tx(bar_full(s), 2u * L::x_stage);
                     const uint32_t dst = x_smem + s * L::x_stage;
@@ -259,6 +274,7 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
         if (crank == 0) {
             constexpr uint32_t idesc = umma_idesc_f16(256, TILE_M, kBF16);
             uint32_t c = 0, it = 0;
+            uint32_t full_ok = 0u;
             for (int tile = slot; tile < num_tiles; tile += nslots, it++) {
                 const uint32_t ab = it % ACC;
                 mbar_wait(bar_acc_empty(ab), ((it / ACC) & 1u) ^ 1u, cta_abort, p.dev_err, 202);
@@ -266,8 +282,12 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
                 const uint32_t tmem_d = tmem_base + ab * TILE_M;
                 for (int ks = 0; ks < p.kst; ks++, c++) {
                     const int s = c % S;
-                    mbar_wait(bar_full(s), (c / S) & 1u, cta_abort, p.dev_err, 203);
+                    WQ4_TL(1, c, 0);
+                    if (!full_ok) mbar_wait(bar_full(s), (c / S) & 1u, cta_abort, p.dev_err, 203);
+                    WQ4_TL(1, c, 1);
                     tc_fence_after();
+                    // probe the next stage's barrier now: the ~200 clk probe latency runs under this stage's MMA issue
+                    full_ok = mbar_test_wait(bar_full((c + 1) % S), ((c + 1) / S) & 1u);
                     const uint64_t bdesc0 = umma_smem_desc_sw128(x_smem + s * L::x_stage);
                     const uint64_t bdesc1 = umma_smem_desc_sw128(x_smem + s * L::x_stage + L::x_box);
                     const uint32_t a_tmem = tmem_base + L::a_col0 + (c % L::AST) * kAColsPerStage;
@@ -282,6 +302,7 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
                         if (ks == p.kst - 1) umma_commit2_mcast(bar_acc_full(ab), (uint16_t)0x3);
                     }
                     __syncwarp();
+                    WQ4_TL(1, c, 2);
                 }
             }
         }
@@ -316,15 +337,26 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
         const uint32_t full_leader0 = mapa_u32(bar_full(0), 0u);
         const int my_tiles = (num_tiles - slot + nslots - 1) / nslots;
         const uint32_t total = (uint32_t)(my_tiles > 0 ? my_tiles : 0) * (uint32_t)p.kst;
+        // An mbarrier probe costs ~200 clk even when the phase completed long ago (timeline in profiles/), and this loop
+        // has two of them per stage.  Both are therefore issued one step early -- the raw slab of stage c+1 and the TMEM
+        // slot of stage c are probed (non-blocking test_wait) before the dequant arithmetic of stage c -- and only waited
+        // on if that early probe failed, which in steady state it does not.
+        uint32_t raw_ok = 0u;
         for (uint32_t c = 0; c < total; c++) {
             const int rs = c % RS;
-            mbar_wait(bar_raw_full(rs), (c / RS) & 1u, cta_abort, p.dev_err, 206);
+            if (dw == 0) WQ4_TL(2, c, 0);
+            if (!raw_ok) mbar_wait(bar_raw_full(rs), (c / RS) & 1u, cta_abort, p.dev_err, 206);
+            if (dw == 0) WQ4_TL(2, c, 1);
             const uint8_t *raw = base_ptr + L::raw_off + rs * kRawStage;
             const int e0 = (2 * half) * WQ4_PANEL_ROWS + r, e1 = e0 + WQ4_PANEL_ROWS;
             const uint4 q0 = *reinterpret_cast<const uint4 *>(raw + e0 * 16);
             const uint4 q1 = *reinterpret_cast<const uint4 *>(raw + e1 * 16);
             const uint32_t d0 = scale_pair<kBF16>(*reinterpret_cast<const uint16_t *>(raw + kRawNib + e0 * 2));
             const uint32_t d1 = scale_pair<kBF16>(*reinterpret_cast<const uint16_t *>(raw + kRawNib + e1 * 2));
+            raw_ok = (c + 1 < total) ? mbar_test_wait(bar_raw_full((c + 1) % RS), ((c + 1) / RS) & 1u) : 1u;
+            uint32_t slot_ok = 1u;
+            const uint32_t pc = c - L::AST;           // slot c % AST is free once the MMA of stage c - AST has completed
+            if (c >= (uint32_t)L::AST) slot_ok = mbar_test_wait(bar_empty(pc % S), (pc / S) & 1u);
             uint32_t v[32];
             dequant_word2<kBF16>(q0.x, d0, v + 0);
             dequant_word2<kBF16>(q0.y, d0, v + 4);
@@ -337,13 +369,14 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
             __syncwarp();                             // every lane has consumed its raw bytes
             if (elect_one()) mbar_arrive(bar_raw_empty(rs));
             const int s = c % S;
-            if (c >= (uint32_t)L::AST) {              // slot c % AST is free once the MMA of stage c - AST has completed
-                const uint32_t pc = c - L::AST;
-                mbar_wait(bar_empty(pc % S), (pc / S) & 1u, cta_abort, p.dev_err, 207);
-            }
+            if (dw == 0) WQ4_TL(2, c, 2);
+            if (!slot_ok) mbar_wait(bar_empty(pc % S), (pc / S) & 1u, cta_abort, p.dev_err, 207);
+            __syncwarp();
+            if (dw == 0) WQ4_TL(2, c, 3);
             tc_fence_after();
             tmem_st_32x32b_x32(my_tmem + (c % L::AST) * kAColsPerStage, v);
             tmem_st_wait();
+            if (dw == 0) WQ4_TL(3, c, 0);
             tc_fence_before();
             __syncwarp();
             if (elect_one()) mbar_arrive_cluster(full_leader0 + 8u * s);
@@ -359,6 +392,7 @@ q4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const Gemm2Params p)
         else if (f_gelu && !f_res && !f_y32 && f_y16) mode = 2;    // fc1 + GELU -> f16
         else if (!f_gelu && f_res && f_y32 && !f_y16) mode = 3;    // out-proj / fc2 + residual
         const uint32_t acc_empty_leader0 = mapa_u32(bar_acc_empty(0), 0u);
+        grid_dep_wait();       // residual reads and output writes must follow the predecessor grid
         uint32_t it = 0;
         for (int tile = slot; tile < num_tiles; tile += nslots, it++) {
             const int panel = (tile % p.npairs) * 2 + crank;
@@ -469,19 +503,26 @@ int32_t launch2(const CUtensorMap &tx, const Gemm2Params &p, int device, cudaStr
     cfg.blockDim = dim3(kThreads2, 1, 1);
     cfg.dynamicSmemBytes = L::alloc;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = wq4_pdl_enabled() ? 2 : 1;
     WQ4_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, p));
     wq4_count_launch();
     return WQ4_OK;
 }
 
 }  // namespace
+
+// Debug hook (not part of the drop-in surface): dev_ptr = 4 roles x 64 stages x 4 int64 clock64 stamps of CTA 0 of the
+// following GEMM launches (role 0 X producer, 1 MMA issuer, 2/3 dequant warp 0); NULL disables.
+static long long *g_gemm_timeline_host = nullptr;
+extern "C" WQ4_API void wq4_debug_gemm_timeline(void *dev_ptr) { g_gemm_timeline_host = reinterpret_cast<long long *>(dev_ptr); }
 
 // Row-tile heuristic for the CTA-pair kernel.  Per pair tile the time is ~ max(MMA, dequant) per K stage plus a
 // fixed fill/drain part; cost model in units of "activation rows": waves * (max(tile_m, 150) + 48), fitted to
@@ -546,6 +587,7 @@ int32_t wq4_launch_gemm2_q4(const LinearArgs &a, int tile_m)
     p.bias = a.bias; p.residual = a.residual; p.y32 = a.y_f32; p.y16 = a.y_f16;
     p.ldy = w->n;
     p.flags = a.flags; p.dev_err = wq4_error_flag_ptr(w->device);
+    p.timeline = g_gemm_timeline_host;
     if (!p.dev_err) return WQ4_ERR_CUDA;
     WqProfScope prof(WQ4_PROF_GEMM_Q4, 2.0 * (double)a.rows * (double)w->n * (double)w->k, a.stream);
 #define WQ4_CASE2(T)                                                                             \

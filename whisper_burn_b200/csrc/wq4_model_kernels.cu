@@ -7,6 +7,7 @@
 #include <cstdlib>
 
 #include "wq4_common.cuh"
+#include "wq4_ptx.cuh"
 #include "wq4_model.cuh"
 
 namespace {
@@ -42,6 +43,8 @@ __global__ void __launch_bounds__(128) layernorm_kernel(const float *__restrict_
     constexpr int D = NI * 128;
     const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
+    ptx::grid_dep_launch();     // PDL (wq4_ptx.cuh): successor may be scheduled; we wait for our own predecessor
+    ptx::grid_dep_wait();
     if (row >= rows) return;
     const float4 *xr = reinterpret_cast<const float4 *>(x + (size_t)row * D);
     float4 v[NI];
@@ -534,13 +537,23 @@ int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y3
     dim3 grid((unsigned)((rows + 3) / 4)), block(128);
     __half *h = reinterpret_cast<__half *>(y16);
     WqProfScope prof(WQ4_PROF_LAYERNORM, (double)rows * (double)D * (4.0 + (y32 ? 4.0 : 0.0) + (y16 ? 2.0 : 0.0)), st);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = wq4_pdl_enabled() ? 1 : 0;
+    const int irows = (int)rows;
     switch (D) {
-    case 256: layernorm_kernel<2><<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows); break;
-    case 384: layernorm_kernel<3><<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows); break;
-    case 512: layernorm_kernel<4><<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows); break;
-    case 768: layernorm_kernel<6><<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows); break;
-    case 1024: layernorm_kernel<8><<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows); break;
-    case 1280: layernorm_kernel<10><<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows); break;
+    case 256: WQ4_CUDA(cudaLaunchKernelEx(&cfg, layernorm_kernel<2>, x, w, b, y32, h, irows)); break;
+    case 384: WQ4_CUDA(cudaLaunchKernelEx(&cfg, layernorm_kernel<3>, x, w, b, y32, h, irows)); break;
+    case 512: WQ4_CUDA(cudaLaunchKernelEx(&cfg, layernorm_kernel<4>, x, w, b, y32, h, irows)); break;
+    case 768: WQ4_CUDA(cudaLaunchKernelEx(&cfg, layernorm_kernel<6>, x, w, b, y32, h, irows)); break;
+    case 1024: WQ4_CUDA(cudaLaunchKernelEx(&cfg, layernorm_kernel<8>, x, w, b, y32, h, irows)); break;
+    case 1280: WQ4_CUDA(cudaLaunchKernelEx(&cfg, layernorm_kernel<10>, x, w, b, y32, h, irows)); break;
     default: layernorm_generic_kernel<<<grid, block, 0, st>>>(x, w, b, y32, h, (int)rows, (int)D); break;
     }
     wq4_count_launch();

@@ -41,6 +41,21 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
         : "memory");
     return ok;
 }
+// Non-blocking probe (try_wait may suspend the thread up to a HW time limit of several microseconds when the phase is
+// not complete; test_wait returns the current state).  Used to probe a barrier one step early so that the ~200 clk
+// round trip of the probe overlaps useful work; the blocking wait is then only entered if the probe failed.
+__device__ __forceinline__ uint32_t mbar_test_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
 
 // Bounded wait.  A pipeline bug must never hang the GPU: after `kSpinLimit` failed probes the
 // waiter raises the CTA-wide abort flag (shared) and the sticky device error flag (global), and
@@ -374,5 +389,12 @@ __device__ __forceinline__ void tmem_st_32x32b_x64(uint32_t taddr, const uint32_
 // Warpgroup register re-allocation (all 4 warps of an aligned warpgroup execute it).
 template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
+// Programmatic dependent launch (PDL): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// start while its predecessor in the stream is still running; grid_dep_wait() blocks until the predecessor grid has
+// completed and its writes are visible (no-op without the attribute); grid_dep_launch() lets the successor's CTAs be
+// scheduled as soon as every CTA of this grid has issued it (they still park in their own grid_dep_wait()).
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 }  // namespace ptx
