@@ -120,3 +120,43 @@ def test_transcribe_tokens_match_oracle(tiny, lang):
         assert ids[b][:n] == want[:n]
         print(f"   compared {n} leading tokens, {len(set(want[:n]))} distinct")
         assert n >= 1
+
+
+@pytest.fixture(scope="module")
+def tiny8():
+    cfg = wn.tiny_config(d=256, heads=4, enc_layers=1, dec_layers=2, n_audio_ctx=1500)
+    blob = wn.state_to_gguf(wn.random_state(cfg, seed=9))
+    oracle = wn.WhisperOracle(blob, cfg)
+    model = wb.load_whisper_from_gguf(blob, _cfg_pair(cfg), DEV)
+    model.reserve(8)
+    return cfg, oracle, model
+
+
+@pytest.mark.parametrize("batch", [1, 2, 4, 5, 8])
+def test_decode_step_kernel_every_batch_size(tiny8, batch):
+    """The one-kernel decode step (csrc/wq4_decode.cu, templates R = 1, 2, 4, 8; batch 5 runs the R = 8 code with three
+    idle rows) against the oracle clip by clip: different audio and different tokens per clip, so a wrong batch index,
+    cache row or split-KV segment shows up as a logit mismatch."""
+    cfg, oracle, model = tiny8
+    mel = wn.synthetic_mel(batch, cfg.n_mels, 3000, seed=40 + batch)
+    model.encode(torch.from_numpy(mel).to(DEV), want_output=False)
+    encs = [oracle.encode(mel[b:b + 1]) for b in range(batch)]
+    caches = [oracle.new_cache() for _ in range(batch)]
+    prompts = [[wn.SOT, 50259 + b, cfg.transcribe_token(), cfg.no_timestamps_token()] for b in range(batch)]
+    want = [oracle.forward_prompt(prompts[b], encs[b], caches[b]) for b in range(batch)]
+    got = model.decoder_pass(prompts, 0, 0, recompute_cross=True).cpu().numpy()
+    for b in range(batch):
+        assert rel_err(got[b], want[b]) < 1e-2, ("prompt", b)
+    toks = [int(w.argmax()) for w in want]
+    pos = 4
+    worst = 0.0
+    for step in range(10):
+        want = [oracle.decode_step(toks[b], pos, encs[b], caches[b]) for b in range(batch)]
+        got = model.decoder_pass([[t] for t in toks], pos, pos).cpu().numpy()
+        for b in range(batch):
+            e = rel_err(got[b], want[b])
+            worst = max(worst, e)
+            assert e < 1e-2, (step, b, e)
+        toks = [(int(w.argmax()) + 17 * b) % 50000 for b, w in enumerate(want)]     # distinct, deterministic
+        pos += 1
+    print(f"batch {batch}: worst logit rel err over 10 steps {worst:.2e}")
