@@ -11,6 +11,10 @@ pub struct wq4_conv1d {
     _private: [u8; 0],
 }
 #[repr(C)]
+pub struct wq4_logmel {
+    _private: [u8; 0],
+}
+#[repr(C)]
 pub struct wq4_whisper {
     _private: [u8; 0],
 }
@@ -77,6 +81,11 @@ extern "C" {
     pub fn wq4_conv1d_forward(c: *const wq4_conv1d, x_dev: *const f32, y_dev: *mut f32, b: i64, t: i64,
                               padding: i64, stride: i64, flags: u32, workspace_dev: *mut c_void,
                               workspace_bytes: usize, stream: wq4_stream) -> i32;
+
+    pub fn wq4_logmel_create(n_mels: i32, device: i32, stream: wq4_stream, out: *mut *mut wq4_logmel) -> i32;
+    pub fn wq4_logmel_destroy(m: *mut wq4_logmel) -> i32;
+    pub fn wq4_logmel_forward(m: *const wq4_logmel, pcm_dev: *const f32, batch: i64, n_samples: i64,
+                              mel_dev: *mut f32, stream: wq4_stream) -> i32;
 
     pub fn wq4_gguf_probe(data: *const u8, nbytes: usize, version: *mut u32, tensor_count: *mut u64,
                           data_offset: *mut u64) -> i32;

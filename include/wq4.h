@@ -182,6 +182,18 @@ WQ4_API int32_t wq4_whisper_decoder_pass(wq4_whisper *m, const int32_t *tokens_h
 WQ4_API int32_t wq4_whisper_decode_step_device(wq4_whisper *m, int64_t batch, int64_t position,
                                                int64_t kv_len, wq4_stream stream);
 
+/* ---- Log-mel front end (batched transcribe front-end) ----------------- */
+/* MelSpectrogram::compute_log (src/audio/mel.rs:105-157: reflect-padded 400-point STFT, periodic Hann, hop 160,
+ * |X|^2, Slaney filterbank mel.rs:270-312, log10(max(.,1e-10)), clamp to max-8, (.+4)/4) plus the framing of
+ * src/transcribe.rs:46-82 (clip padded with zeros / truncated to 480000 samples, output transposed to
+ * [n_mels, 3000]), for a batch of clips on the device. */
+typedef struct wq4_logmel wq4_logmel;
+WQ4_API int32_t wq4_logmel_create(int32_t n_mels, int32_t device, wq4_stream stream, wq4_logmel **out);
+WQ4_API int32_t wq4_logmel_destroy(wq4_logmel *m);
+/* pcm_dev [batch][n_samples] f32, 16 kHz mono -> mel_dev [batch][n_mels][3000] f32 (the encoder's input). */
+WQ4_API int32_t wq4_logmel_forward(const wq4_logmel *m, const float *pcm_dev, int64_t batch,
+                                   int64_t n_samples, float *mel_dev, wq4_stream stream);
+
 /* ---- Introspection used by bench.py / tests ------------------------------------------- */
 /* Which kernel family a [rows,K]x[N,K]^T call dispatches to: 0 = GEMV (CUDA cores),
  * 1 = tcgen05 GEMM.  `tile_m` receives the GEMM row tile (0 for GEMV). */
