@@ -160,3 +160,15 @@ def test_decode_step_kernel_every_batch_size(tiny8, batch):
         toks = [(int(w.argmax()) + 17 * b) % 50000 for b, w in enumerate(want)]     # distinct, deterministic
         pos += 1
     print(f"batch {batch}: worst logit rel err over 10 steps {worst:.2e}")
+
+
+def test_load_from_path_equals_load_from_memory(golden_dir):
+    """wq4_whisper_load_gguf (mmap of the file) and wq4_whisper_load_gguf_memory give the same model."""
+    path = golden_dir / "tiny_whisper.gguf"
+    cfg = wn.WhisperConfig(80, 32, 256, 4, 1, 16, 256, 4, 1, 64, 99)
+    a = wb.load_whisper_from_gguf(str(path), _cfg_pair(cfg), DEV)
+    b = wb.load_whisper_from_gguf(path.read_bytes(), _cfg_pair(cfg), DEV)
+    mel = torch.from_numpy(wn.synthetic_mel(2, 80, 64, seed=3)).to(DEV)
+    assert torch.equal(a.encode(mel), b.encode(mel))
+    with pytest.raises(wb.Wq4Error):
+        wb.load_whisper_from_gguf(str(golden_dir / "does_not_exist.gguf"), _cfg_pair(cfg), DEV)

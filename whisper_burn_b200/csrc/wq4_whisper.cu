@@ -18,6 +18,11 @@
 #include <string>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include "wq4_common.cuh"
 #include "wq4_model.cuh"
 
@@ -584,16 +589,21 @@ int32_t wq4_whisper_load_gguf_memory(const uint8_t *data, size_t nbytes, const w
 int32_t wq4_whisper_load_gguf(const char *path, const wq4_whisper_config *cfg, int32_t device, wq4_whisper **out)
 {
     if (!path || !cfg || !out) { wq4_set_error("wq4_whisper_load_gguf: null argument"); return WQ4_ERR_INVALID; }
-    FILE *f = fopen(path, "rb");
-    if (!f) { wq4_set_error("Failed to open GGUF file: %s", path); return WQ4_ERR_INVALID; }   // loader.rs:31-32
-    fseek(f, 0, SEEK_END);
-    long n = ftell(f);
-    fseek(f, 0, SEEK_SET);
-    std::vector<uint8_t> buf((size_t)n);
-    size_t got = fread(buf.data(), 1, (size_t)n, f);
-    fclose(f);
-    if (got != (size_t)n) { wq4_set_error("short read on %s", path); return WQ4_ERR_INVALID; }
-    return wq4_whisper_load_gguf_memory(buf.data(), buf.size(), cfg, device, out);
+    // The file is mapped, not read: tensor bytes go from the page cache straight into the driver's staging copies
+    // (the reference copies every tensor twice on the host first: reader.rs:220-221, tensor.rs:54-61).
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) { wq4_set_error("Failed to open GGUF file: %s", path); return WQ4_ERR_INVALID; }   // loader.rs:31-32
+    struct stat sb;
+    if (fstat(fd, &sb) != 0 || sb.st_size <= 0) { close(fd); wq4_set_error("cannot stat %s", path); return WQ4_ERR_INVALID; }
+    const size_t n = (size_t)sb.st_size;
+    void *map = mmap(nullptr, n, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (map == MAP_FAILED) { wq4_set_error("mmap failed on %s", path); return WQ4_ERR_INVALID; }
+    madvise(map, n, MADV_SEQUENTIAL);
+    madvise(map, n, MADV_WILLNEED);
+    const int32_t st = wq4_whisper_load_gguf_memory(static_cast<const uint8_t *>(map), n, cfg, device, out);
+    munmap(map, n);
+    return st;
 }
 
 int32_t wq4_whisper_destroy(wq4_whisper *m)
