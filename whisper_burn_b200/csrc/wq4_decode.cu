@@ -165,7 +165,7 @@ __device__ __forceinline__ void epi_apply(const EpiCtx &e, int m, int n, float v
 }
 
 template <int R>
-__device__ __noinline__ void gemv_phase(const DecWeight w, const float *xs, float *red, int nrows, const EpiCtx epi)
+__device__ __noinline__ void gemv_phase_fma(const DecWeight w, const float *xs, float *red, int nrows, const EpiCtx epi)
 {
     const int tid = threadIdx.x;
     const int rpc = w.rpc, kb = w.kb, K = w.k;
@@ -237,6 +237,124 @@ __device__ __noinline__ void gemv_phase(const DecWeight w, const float *xs, floa
         }
     }
     __syncthreads();
+}
+
+// Tensor-core form of the GEMV phase for R >= 4 rows (mma.sync.m16n8k16, f16 operands, f32 accumulate): the batch rows
+// are the MMA's N = 8 columns, 16 weight rows its M.  On the CUDA cores the phase costs R FMAs per weight and is
+// FMA/LDS bound from R = 4 up (~15-20 us per phase at R = 8 against ~5 us at R = 1); here a weight costs one half2 op
+// to dequantise and the phase is back to being bound by the weight stream and the barrier.
+//   * warp w owns the k-blocks w, w+16, ... of ALL of this CTA's rows (groups of 16 rows, G <= 3);
+//   * A fragment: the device word layout (wq4_common.cuh) already holds K-consecutive pairs (e0|e1, e2|e3, ...) in
+//     half2-ready bit positions, so lane%4 selects its pair by a shift and a mask: rows lane/4 and lane/4+8,
+//     k = 2*(lane%4)+{0,1} (+8) of the 16-wide step; (nib - 8) exact in f16, then one rounding by the block scale;
+//   * B fragment: x[n = lane/4][k] from shared memory (f32 -> f16x2);
+//   * partial 16 x 8 tiles of the 16 warps are summed through `red` in a fixed order (deterministic).
+__device__ __forceinline__ void mma_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1)
+{
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+constexpr int kMmaMaxGroups = 3;
+constexpr int kMmaRedFloats = (kDT / 32) * kMmaMaxGroups * 16 * 8;
+
+template <int R>
+__device__ __noinline__ void gemv_phase_mma(const DecWeight w, const float *xs, float *red, int nrows, const EpiCtx epi)
+{
+    static_assert(R == 4 || R == 8, "mma GEMV: 4 or 8 batch rows");
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int rpc = w.rpc, kb = w.kb, K = w.k;
+    const int row0 = blockIdx.x * rpc;
+    const int G = (rpc + 15) >> 4;
+    const int j = lane & 3, n = lane >> 2;                 // pair index inside the word / batch row (B column)
+    // bias (+ residual) of the output this thread will finish, fetched before the weight stream
+    float pre[2] = {0.0f, 0.0f};
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const int o = tid + i * kDT;
+        const int s2 = o / R, m = o - s2 * R, nn = row0 + s2;
+        if (o < rpc * R && nn < w.n && m < nrows) {
+            float v = w.bias ? __ldg(w.bias + nn) : 0.0f;
+            if (epi.kind == EPI_RESID) v += __ldcg(epi.dst + (size_t)m * epi.ld + nn);
+            pre[i] = v;
+        }
+    }
+    float acc[kMmaMaxGroups][4];
+#pragma unroll
+    for (int g = 0; g < kMmaMaxGroups; g++) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.0f;
+    if (row0 < w.n) {
+        const uint32_t sh = (uint32_t)(j >> 1) * 8u;
+        const uint32_t mask = (j & 1) ? 0x00F000F0u : 0x000F000Fu;
+        const __half2 mul = (j & 1) ? __floats2half2_rn(0.0625f, 0.0625f) : __floats2half2_rn(1.0f, 1.0f);
+        const __half2 add = (j & 1) ? __floats2half2_rn(-72.0f, -72.0f) : __floats2half2_rn(-1032.0f, -1032.0f);
+        const size_t cbase = (size_t)blockIdx.x * kb * rpc;
+        const float *xrow = xs + (size_t)(n < R ? n : 0) * K;
+        auto frag = [&](uint32_t word, __half2 d2) -> uint32_t {
+            uint32_t t = ((word >> sh) & mask) | 0x64006400u;
+            __half2 v = __hmul2(__hfma2(*reinterpret_cast<__half2 *>(&t), mul, add), d2);
+            return *reinterpret_cast<uint32_t *>(&v);
+        };
+        for (int kbi = warp; kbi < kb; kbi += kDT / 32) {
+            // B fragments of the two 16-wide steps of this block
+            uint32_t bfrag[2][2];
+#pragma unroll
+            for (int s2 = 0; s2 < 2; s2++) {
+#pragma unroll
+                for (int h2 = 0; h2 < 2; h2++) {
+                    float2 xv = make_float2(0.0f, 0.0f);
+                    if (n < R) xv = *reinterpret_cast<const float2 *>(xrow + kbi * 32 + s2 * 16 + h2 * 8 + 2 * j);
+                    const __half2 hv = __floats2half2_rn(xv.x, xv.y);
+                    bfrag[s2][h2] = *reinterpret_cast<const uint32_t *>(&hv);
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < kMmaMaxGroups; g++) {
+                if (g < G) {
+                    const int r0 = g * 16 + n, r1 = r0 + 8;
+                    uint4 q0 = make_uint4(0x88888888u, 0x88888888u, 0x88888888u, 0x88888888u), q1 = q0;
+                    __half d0 = __ushort_as_half((unsigned short)0), d1 = d0;
+                    if (r0 < rpc) { q0 = ldg_stream16(w.nib + cbase + (size_t)kbi * rpc + r0); d0 = __ldg(w.scl + cbase + (size_t)kbi * rpc + r0); }
+                    if (r1 < rpc) { q1 = ldg_stream16(w.nib + cbase + (size_t)kbi * rpc + r1); d1 = __ldg(w.scl + cbase + (size_t)kbi * rpc + r1); }
+                    const __half2 d02 = __half2half2(d0), d12 = __half2half2(d1);
+                    mma_16816(acc[g], frag(q0.x, d02), frag(q1.x, d12), frag(q0.y, d02), frag(q1.y, d12), bfrag[0][0], bfrag[0][1]);
+                    mma_16816(acc[g], frag(q0.z, d02), frag(q1.z, d12), frag(q0.w, d02), frag(q1.w, d12), bfrag[1][0], bfrag[1][1]);
+                }
+            }
+        }
+    }
+    // C fragment: c0,c1 -> (row n, batch 2j, 2j+1); c2,c3 -> (row n + 8, same batch columns)
+#pragma unroll
+    for (int g = 0; g < kMmaMaxGroups; g++) {
+        if (g < G) {
+            float *t = red + ((size_t)(warp * kMmaMaxGroups + g) * 16) * 8;
+            *reinterpret_cast<float2 *>(t + n * 8 + 2 * j) = make_float2(acc[g][0], acc[g][1]);
+            *reinterpret_cast<float2 *>(t + (n + 8) * 8 + 2 * j) = make_float2(acc[g][2], acc[g][3]);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const int o = tid + i * kDT;
+        const int s2 = o / R, m = o - s2 * R, nn = row0 + s2;
+        if (o < rpc * R && nn < w.n && m < nrows) {
+            const int g = s2 >> 4, rr = s2 & 15;
+            float s = 0.0f;
+#pragma unroll
+            for (int w2 = 0; w2 < kDT / 32; w2++) s += red[((size_t)(w2 * kMmaMaxGroups + g) * 16 + rr) * 8 + m];
+            epi_apply(epi, m, nn, s + pre[i]);
+        }
+    }
+    __syncthreads();
+}
+
+template <int R>
+__device__ __forceinline__ void gemv_phase(const DecWeight w, const float *xs, float *red, int nrows, const EpiCtx epi)
+{
+    if constexpr (R >= 4) {
+        if (w.rpc <= 16 * kMmaMaxGroups && w.rpc * R <= 2 * kDT) { gemv_phase_mma<R>(w, xs, red, nrows, epi); return; }
+    }
+    gemv_phase_fma<R>(w, xs, red, nrows, epi);
 }
 
 // LayerNorm::forward (src/model/layers.rs:23-31) of R rows of a global [R][D] f32 matrix into shared memory.
@@ -796,7 +914,8 @@ __global__ void logits_matrix_kernel(const float *__restrict__ emb, uint4 *__res
 template <int R>
 int32_t launch_decode(const DecodeStepArgs &a, int device, cudaStream_t st)
 {
-    const size_t smem = ((size_t)R * (a.F > a.D ? a.F : a.D) + (size_t)kDT * R + 1088) * sizeof(float);
+    const size_t red_floats = (size_t)kDT * R > (size_t)kMmaRedFloats ? (size_t)kDT * R : (size_t)kMmaRedFloats;
+    const size_t smem = ((size_t)R * (a.F > a.D ? a.F : a.D) + red_floats + 1088) * sizeof(float);
     auto kern = decode_step_kernel<R>;
     static bool attr_done[64] = {};
     if (device < 0 || device >= 64 || !attr_done[device]) {
