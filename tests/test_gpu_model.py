@@ -128,14 +128,14 @@ def tiny8():
     blob = wn.state_to_gguf(wn.random_state(cfg, seed=9))
     oracle = wn.WhisperOracle(blob, cfg)
     model = wb.load_whisper_from_gguf(blob, _cfg_pair(cfg), DEV)
-    model.reserve(8)
+    model.reserve(19)
     return cfg, oracle, model
 
 
-@pytest.mark.parametrize("batch", [1, 2, 4, 5, 8])
+@pytest.mark.parametrize("batch", [1, 2, 4, 5, 8, 11, 19])
 def test_decode_step_kernel_every_batch_size(tiny8, batch):
     """The one-kernel decode step (csrc/wq4_decode.cu, templates R = 1, 2, 4, 8; batch 5 runs the R = 8 code with three
-    idle rows) against the oracle clip by clip: different audio and different tokens per clip, so a wrong batch index,
+    idle rows; batches 11 and 19 run it once per group of 8 clips on offset cache pointers) against the oracle clip by clip: different audio and different tokens per clip, so a wrong batch index,
     cache row or split-KV segment shows up as a logit mismatch."""
     cfg, oracle, model = tiny8
     mel = wn.synthetic_mel(batch, cfg.n_mels, 3000, seed=40 + batch)

@@ -728,8 +728,8 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
 
     for (int l = 0; l < a.n_layers; l++) {
         const DecLayerW &L = a.layers[l];   // kernel-parameter constant bank
-        __half *sk = a.self_k + (size_t)l * B * a.ctx * D, *sv = a.self_v + (size_t)l * B * a.ctx * D;
-        const __half *ck = a.cross_kv + (size_t)l * B * a.T_enc * 2 * D;
+        __half *sk = a.self_k + (size_t)l * a.kv_clips * a.ctx * D, *sv = a.self_v + (size_t)l * a.kv_clips * a.ctx * D;
+        const __half *ck = a.cross_kv + (size_t)l * a.kv_clips * a.T_enc * 2 * D;
 
         // P1: LN1 -> fused q|k|v projection; q -> a.q, k/v -> f16 cache row kv_len-1 (decoder.rs:84-92, attention.rs:99-113)
         prefetch_weight(L.out, nullptr, nullptr, D);

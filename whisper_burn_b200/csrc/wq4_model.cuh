@@ -61,6 +61,7 @@ struct DecodeStepArgs {           // passed BY VALUE: the per-layer table sits i
     float *arg_scratch;           // [grid][B][2]
     unsigned *barrier;            // grid barrier counter (zeroed before every launch)
     int *dev_err;
+    int kv_clips;          // clips the KV caches were laid out for ([layer][kv_clips][ctx|T_enc][D]); >= B
     long long *timeline;   // debug: kDecTimelineSlots x int64 barrier time stamps, normally NULL
 };
 // Builds the decode layout of a panel-layout tensor (device to device).

@@ -472,29 +472,40 @@ static bool use_decode_kernel()
     return v == 1;
 }
 
-// One decode step for B <= 8 clips as a single persistent kernel (wq4_decode.cu).
+// One decode step as a single persistent kernel per group of up to 8 clips (wq4_decode.cu).  Larger batches run the
+// kernel once per group, back to back on the stream: the caches are laid out [layer][B][..] so a group is a pointer
+// offset, and the kernel takes the layer stride (kv_clips) separately from its own batch.
+constexpr int64_t kDecodeGroup = 8;
+constexpr int64_t kDecodeGroupedMax = 24;     // beyond this the per-op path (weights read once per step) is faster
+
 int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
 {
     if (m->dec.size() > (size_t)kDecMaxLayers) { wq4_set_error("decode step kernel: more than %d decoder layers", kDecMaxLayers); return WQ4_ERR_UNSUPPORTED; }
-    DecodeStepArgs a = {};
-    for (size_t l = 0; l < m->dec.size(); l++) a.layers[l] = m->dec_w_host[l];
-    a.n_layers = (int)m->dec.size(); a.B = (int)B; a.D = (int)m->D; a.F = (int)m->F;
-    a.H = m->cfg.n_text_head; a.V = (int)m->V; a.ctx = m->cfg.n_text_ctx; a.T_enc = (int)m->T_enc;
-    a.tokens = m->d_tokens; a.tok_emb = m->tok_emb; a.tok_emb16t = m->tok_emb16t; a.Vp = (int)m->Vp; a.pos_emb = m->dec_pos;
-    a.emb_pos = (int)emb_pos; a.kv_len = (int)kv_pos0;
-    a.x = m->dx; a.q = m->dq; a.h = m->dh; a.part = m->att_part;
-    a.self_k = m->self_k; a.self_v = m->self_v; a.cross_kv = m->cross_kv;
-    a.lnfw = m->ln.w; a.lnfb = m->ln.b; a.logits = m->logits;
-    a.arg_lo = arg ? arg->lo : 0; a.arg_hi = arg ? arg->hi : 0; a.suppress = arg ? arg->suppress : nullptr;
-    a.next_out = arg ? arg->out : nullptr; a.arg_scratch = m->arg_scratch; a.barrier = m->grid_bar;
-    a.dev_err = wq4_error_flag_ptr(m->device);
-    if (!a.dev_err) return WQ4_ERR_CUDA;
-    return wq4m_decode_step(a, m->device, st);
+    const int64_t D = m->D, F = m->F, ctx = m->cfg.n_text_ctx;
+    for (int64_t g0 = 0; g0 < B; g0 += kDecodeGroup) {
+        const int64_t gb = B - g0 < kDecodeGroup ? B - g0 : kDecodeGroup;
+        DecodeStepArgs a = {};
+        for (size_t l = 0; l < m->dec.size(); l++) a.layers[l] = m->dec_w_host[l];
+        a.n_layers = (int)m->dec.size(); a.B = (int)gb; a.kv_clips = (int)B; a.D = (int)D; a.F = (int)F;
+        a.H = m->cfg.n_text_head; a.V = (int)m->V; a.ctx = (int)ctx; a.T_enc = (int)m->T_enc;
+        a.tokens = m->d_tokens + g0; a.tok_emb = m->tok_emb; a.tok_emb16t = m->tok_emb16t; a.Vp = (int)m->Vp; a.pos_emb = m->dec_pos;
+        a.emb_pos = (int)emb_pos; a.kv_len = (int)kv_pos0;
+        a.x = m->dx + g0 * D; a.q = m->dq + g0 * D; a.h = m->dh + g0 * F; a.part = m->att_part;
+        a.self_k = m->self_k + g0 * ctx * D; a.self_v = m->self_v + g0 * ctx * D;
+        a.cross_kv = m->cross_kv + g0 * m->T_enc * 2 * D;
+        a.lnfw = m->ln.w; a.lnfb = m->ln.b; a.logits = m->logits + g0 * m->V;
+        a.arg_lo = arg ? arg->lo : 0; a.arg_hi = arg ? arg->hi : 0; a.suppress = (arg && arg->suppress) ? arg->suppress + g0 : nullptr;
+        a.next_out = (arg && arg->out) ? arg->out + g0 : nullptr; a.arg_scratch = m->arg_scratch; a.barrier = m->grid_bar;
+        a.dev_err = wq4_error_flag_ptr(m->device);
+        if (!a.dev_err) return WQ4_ERR_CUDA;
+        CHK(wq4m_decode_step(a, m->device, st));
+    }
+    return WQ4_OK;
 }
 
 int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
 {
-    if (q_len == 1 && B <= 8 && m->decode_kernel_ready && use_decode_kernel() && m->dec.size() <= (size_t)kDecMaxLayers) {
+    if (q_len == 1 && B <= kDecodeGroupedMax && m->decode_kernel_ready && use_decode_kernel() && m->dec.size() <= (size_t)kDecMaxLayers) {
         if (kv_pos0 + 1 > m->cfg.n_text_ctx || emb_pos0 + 1 > m->cfg.n_text_ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
         return decode_step_fused(m, B, emb_pos0, kv_pos0, arg, st);
     }
