@@ -165,10 +165,9 @@ def run_reference(args):
     from oracle import q4
     cfg = preset(args.model)
     threads = q4.host_cores()
-    layers = 1
+    t1 = cpu_sample(cfg, 1, threads)                       # warm-up and sizing: one layer
+    layers = max(1, min(cfg.n_audio_layer, int(round(4.0 / max(t1, 1e-3)))))    # ~4 s of CPU work per step
     frac = layers / cfg.n_audio_layer
-    for _ in range(args.warmup if args.warmup < 2 else 1):
-        cpu_sample(cfg, layers, threads)
     times = [cpu_sample(cfg, layers, threads) for _ in range(max(1, min(args.steps, 5)))]
     t = statistics.median(times)
     clips_per_s = frac / t
@@ -177,7 +176,10 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": clips_per_s, "unit": UNIT, "n_gpus": args.gpus,
             "steps": len(times), "warmup": args.warmup, "ms_per_step": t / frac * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"whisper-{args.model} encoder, 1x30s mel per step, random-init Q4_0 weights (CPU port of the reference path)"},
+            "config": {"workload": f"whisper-{args.model} encoder, 1x30s mel [1,{cfg.n_mels},{2 * cfg.n_audio_ctx}] per GPU per step, "
+                                   f"random-init Q4_0 weights", "batch_per_gpu": 1,
+                       "arm": "reference's CPU path for the Q4 linears (C port, oracle/q4_oracle.c) on all host threads; each step is a "
+                              f"bounded sample of {layers} of {cfg.n_audio_layer} encoder layers scaled to the whole clip"},
             "cpu_baseline": {"value": clips_per_s, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": clips_per_s, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -334,12 +336,14 @@ def run_own(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         from oracle import q4
         threads = q4.host_cores()
-        t = cpu_sample(cfg, 1, threads)
-        frac = 1.0 / cfg.n_audio_layer
+        t1 = cpu_sample(cfg, 1, threads)                   # warm-up and sizing
+        n_l = max(1, min(cfg.n_audio_layer, int(round(12.0 / max(t1, 1e-3)))))   # ~12 s of CPU work
+        t = cpu_sample(cfg, n_l, threads)
+        frac = n_l / cfg.n_audio_layer
         line["cpu_baseline"] = {"value": frac / t, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"fused Q4_0 dequant+matmul (oracle/q4_oracle.c, shader.wgsl:72-89 twin) of the 6 linears of 1 of "
-                                          f"{cfg.n_audio_layer} encoder layers at M=1500, {t:.2f} s, extrapolated x{cfg.n_audio_layer}; "
-                                          f"conv/attention/LN not charged to the CPU"}
+                                "sample": f"fused Q4_0 dequant+matmul (oracle/q4_oracle.c, shader.wgsl:72-89 twin) of the 6 linears of {n_l} of "
+                                          f"{cfg.n_audio_layer} encoder layers at M=1500, {t:.2f} s on {threads} threads, scaled x"
+                                          f"{cfg.n_audio_layer / n_l:.2f}; conv/attention/LN not charged to the CPU"}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
