@@ -128,14 +128,15 @@ def tiny8():
     blob = wn.state_to_gguf(wn.random_state(cfg, seed=9))
     oracle = wn.WhisperOracle(blob, cfg)
     model = wb.load_whisper_from_gguf(blob, _cfg_pair(cfg), DEV)
-    model.reserve(19)
+    model.reserve(26)
     return cfg, oracle, model
 
 
-@pytest.mark.parametrize("batch", [1, 2, 4, 5, 8, 11, 19])
+@pytest.mark.parametrize("batch", [1, 2, 4, 5, 8, 11, 19, 26])
 def test_decode_step_kernel_every_batch_size(tiny8, batch):
     """The one-kernel decode step (csrc/wq4_decode.cu, templates R = 1, 2, 4, 8; batch 5 runs the R = 8 code with three
-    idle rows; batches 11 and 19 run it once per group of 8 clips on offset cache pointers) against the oracle clip by clip: different audio and different tokens per clip, so a wrong batch index,
+    idle rows; batches 11 and 19 run it once per group of 8 clips on offset cache pointers; batch 26 takes the per-op path with the
+    split-KV attention kernel) against the oracle clip by clip: different audio and different tokens per clip, so a wrong batch index,
     cache row or split-KV segment shows up as a logit mismatch."""
     cfg, oracle, model = tiny8
     mel = wn.synthetic_mel(batch, cfg.n_mels, 3000, seed=40 + batch)
@@ -172,3 +173,19 @@ def test_load_from_path_equals_load_from_memory(golden_dir):
     assert torch.equal(a.encode(mel), b.encode(mel))
     with pytest.raises(wb.Wq4Error):
         wb.load_whisper_from_gguf(str(golden_dir / "does_not_exist.gguf"), _cfg_pair(cfg), DEV)
+
+
+def test_grouped_decode_kernel_in_child_process():
+    """Batches 11 and 19 through the single-kernel step run once per group of 8 clips (WQ4_DECODE_GROUP_MAX is read once per
+    process; by default anything beyond one group takes the per-op path, which the in-process cases above cover)."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    if os.environ.get("WQ4_DECODE_GROUP_MAX"):
+        pytest.skip("already inside the child")
+    env = dict(os.environ, WQ4_DECODE_GROUP_MAX="24")
+    r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-q", "-x", "-m", "gpu", "-k",
+                        "every_batch_size and (11 or 19)"], env=env, capture_output=True, text=True, timeout=900)
+    print(r.stdout[-600:], r.stderr[-600:])
+    assert r.returncode == 0 and "2 passed" in r.stdout

@@ -595,6 +595,144 @@ __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc,
     }
 }
 
+// ---- stand-alone form for the per-op decoder path (batches beyond the grouped kernel's reach) -------------------------
+// One query row per clip, f16 KV cache, non-causal: grid (clip*head, split).  Same inner loop as attn_phase (8 lanes per
+// 128-byte key row, 4 keys per lane group in flight, online softmax); with more than one split per unit the last CTA to
+// finish a unit merges its partials ("fix-up" by an arrival counter that it resets), so there is no second launch.
+constexpr int kDaThreads = 256;
+__global__ void __launch_bounds__(kDaThreads)
+dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *__restrict__ kc, const __half *__restrict__ vc,
+                           long long ldkv, long long bstride, float *__restrict__ out, int ldo, int kv_len, int H, int nsplit,
+                           float *__restrict__ part, int *__restrict__ cnt)
+{
+    __shared__ float sm[(kDaThreads / 32) * kPartStride];
+    __shared__ int s_last;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 3, dch = lane & 7;
+    const int u = blockIdx.x, sp = blockIdx.y, h = u % H, b = u / H;
+    const int per = (kv_len + nsplit - 1) / nsplit;
+    const int k0 = sp * per, k1 = min(kv_len, k0 + per);
+    float qv[8];
+    {
+        const float *qp = q + (size_t)b * ldq + h * 64 + dch * 8;
+        const float4 a = *reinterpret_cast<const float4 *>(qp);
+        const float4 c = *(reinterpret_cast<const float4 *>(qp) + 1);
+        qv[0] = a.x * 0.125f; qv[1] = a.y * 0.125f; qv[2] = a.z * 0.125f; qv[3] = a.w * 0.125f;
+        qv[4] = c.x * 0.125f; qv[5] = c.y * 0.125f; qv[6] = c.z * 0.125f; qv[7] = c.w * 0.125f;
+    }
+    const __half *kb_ = kc + (size_t)b * bstride + h * 64 + dch * 8;
+    const __half *vb_ = vc + (size_t)b * bstride + h * 64 + dch * 8;
+    Soft st;
+    st.m = -INFINITY; st.l = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; j++) st.o[j] = 0.0f;
+    constexpr int NT = 4, KW = kDaThreads / 32 * 4;        // keys per t-step over the CTA
+    for (int base0 = k0 + warp * 4; base0 < k1; base0 += KW * NT) {      // warp-uniform trip count (shuffles inside)
+        const int key0 = base0 + g;
+        uint4 kq[NT], vq[NT];
+        bool ok[NT];
+#pragma unroll
+        for (int t = 0; t < NT; t++) {
+            const int key = key0 + t * KW;
+            ok[t] = key < k1;
+            if (ok[t]) {
+                kq[t] = ldg_stream16(reinterpret_cast<const uint4 *>(kb_ + (size_t)key * ldkv));
+                vq[t] = ldg_stream16(reinterpret_cast<const uint4 *>(vb_ + (size_t)key * ldkv));
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < NT; t++) {
+            float sc = 0.0f;
+            if (ok[t]) {
+                const __half2 *hp = reinterpret_cast<const __half2 *>(&kq[t]);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float2 f = __half22float2(hp[e]);
+                    sc = fmaf(qv[2 * e], f.x, sc);
+                    sc = fmaf(qv[2 * e + 1], f.y, sc);
+                }
+            }
+            sc += __shfl_xor_sync(0xffffffffu, sc, 1);
+            sc += __shfl_xor_sync(0xffffffffu, sc, 2);
+            sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+            if (ok[t]) {
+                const float mn = fmaxf(st.m, sc);
+                const float alpha = (st.m == -INFINITY) ? 0.0f : __expf(st.m - mn);
+                const float pw = __expf(sc - mn);
+                st.l = st.l * alpha + pw;
+                const __half2 *vp2 = reinterpret_cast<const __half2 *>(&vq[t]);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float2 f = __half22float2(vp2[e]);
+                    st.o[2 * e] = st.o[2 * e] * alpha + pw * f.x;
+                    st.o[2 * e + 1] = st.o[2 * e + 1] * alpha + pw * f.y;
+                }
+                st.m = mn;
+            }
+        }
+    }
+#pragma unroll
+    for (int off = 8; off <= 16; off <<= 1) {
+        const float m2 = __shfl_xor_sync(0xffffffffu, st.m, off);
+        const float l2 = __shfl_xor_sync(0xffffffffu, st.l, off);
+        float o2[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) o2[j] = __shfl_xor_sync(0xffffffffu, st.o[j], off);
+        soft_merge(st, m2, l2, o2);
+    }
+    if (g == 0) {
+        float *dst = sm + warp * kPartStride;
+        if (dch == 0) { dst[64] = st.m; dst[65] = st.l; }
+#pragma unroll
+        for (int j = 0; j < 8; j++) dst[dch * 8 + j] = st.o[j];
+    }
+    __syncthreads();
+    if (warp != 0) return;
+    // warp 0: merge the warps' partials (fixed order), two output dims per lane
+    float M = -INFINITY;
+    for (int w2 = 0; w2 < kDaThreads / 32; w2++) M = fmaxf(M, sm[w2 * kPartStride + 64]);
+    float Lsum = 0.0f, o0 = 0.0f, o1 = 0.0f;
+    for (int w2 = 0; w2 < kDaThreads / 32; w2++) {
+        const float mw = sm[w2 * kPartStride + 64];
+        const float sc = (mw == -INFINITY) ? 0.0f : __expf(mw - M);
+        Lsum += sc * sm[w2 * kPartStride + 65];
+        o0 += sc * sm[w2 * kPartStride + lane];
+        o1 += sc * sm[w2 * kPartStride + 32 + lane];
+    }
+    float *orow = out + (size_t)b * ldo + h * 64;
+    if (nsplit == 1) {
+        const float inv = 1.0f / Lsum;
+        orow[lane] = o0 * inv;
+        orow[32 + lane] = o1 * inv;
+        return;
+    }
+    float *pd = part + ((size_t)u * nsplit + sp) * kPartStride;
+    if (lane == 0) { pd[64] = M; pd[65] = Lsum; }
+    pd[lane] = o0;
+    pd[32 + lane] = o1;
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) s_last = (atomicAdd(cnt + u, 1) == nsplit - 1) ? 1 : 0;
+    __syncwarp();
+    if (!s_last) return;
+    __threadfence();
+    float Mg = -INFINITY;
+    for (int s2 = 0; s2 < nsplit; s2++) Mg = fmaxf(Mg, __ldcg(part + ((size_t)u * nsplit + s2) * kPartStride + 64));
+    float Lg = 0.0f, a0 = 0.0f, a1 = 0.0f;
+    for (int s2 = 0; s2 < nsplit; s2++) {                   // fixed order: deterministic whichever CTA arrives last
+        const float *ps = part + ((size_t)u * nsplit + s2) * kPartStride;
+        const float mw = __ldcg(ps + 64);
+        const float sc = (mw == -INFINITY) ? 0.0f : __expf(mw - Mg);
+        Lg += sc * __ldcg(ps + 65);
+        a0 += sc * __ldcg(ps + lane);
+        a1 += sc * __ldcg(ps + 32 + lane);
+    }
+    const float inv = 1.0f / Lg;
+    orow[lane] = a0 * inv;
+    orow[32 + lane] = a1 * inv;
+    if (lane == 0) cnt[u] = 0;
+}
+
 // Merge the partials of every (clip, head) into the attention output att[R][D] in shared memory.
 //   stage A: one thread per unit loads its (max, sum) pairs, derives the merge coefficients -> shared memory
 //   stage B: one thread per 4 output columns: coefficient-weighted sum of the partial o vectors (16-byte loads)
@@ -972,6 +1110,29 @@ int32_t wq4m_decw_create(const wq4_tensor *t, const float *bias_dev, int n_cta, 
 int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, int64_t D, cudaStream_t st)
 {
     logits_matrix_kernel<<<4096, 256, 0, st>>>(emb, reinterpret_cast<uint4 *>(dst), (int)V, (int)Vp, (int)D);
+    wq4_count_launch();
+    WQ4_CUDA(cudaGetLastError());
+    return WQ4_OK;
+}
+
+// q [B][ldq] f32, K/V f16 caches (row stride ldkv, clip stride kv_batch_stride elements), out [B][ldo] f32; one query row
+// per clip.  part: >= B*H*nsplit*68 floats, cnt: >= B*H ints (zero; left zero).  nsplit is chosen here.
+int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
+                                 float *out, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part, int64_t part_floats,
+                                 int *cnt, int device, cudaStream_t st)
+{
+    const int64_t units = B * H;
+    if (units < 1 || kv_len < 1) return WQ4_OK;
+    const int sms = wq4_sm_count(device);
+    int64_t ns = (4 * (int64_t)sms + units - 1) / units;        // ~4 CTAs per SM in flight
+    if (ns > 8) ns = 8;
+    while (ns > 1 && (kv_len + ns - 1) / ns < 32) ns--;
+    while (ns > 1 && units * ns * kPartStride > part_floats) ns--;
+    dim3 grid((unsigned)units, (unsigned)ns);
+    dec_attention_split_kernel<<<grid, kDaThreads, 0, st>>>(q, (int)ldq, reinterpret_cast<const __half *>(kc),
+                                                           reinterpret_cast<const __half *>(vc), (long long)ldkv,
+                                                           (long long)kv_batch_stride, out, (int)ldo, (int)kv_len, (int)H, (int)ns,
+                                                           part, cnt);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

@@ -167,6 +167,9 @@ struct wq4_whisper {
     uint4 *tok_emb16t = nullptr;     // [D/8][Vp] f16 chunks
     int64_t Vp = 0;
     float *att_part = nullptr, *arg_scratch = nullptr;
+    float *da_part = nullptr;      // split-KV partials of the per-op decode attention: [B*H][8][68]
+    int *da_cnt = nullptr;         // arrival counters [B*H], zero between launches
+    int64_t da_part_floats = 0;
     unsigned *grid_bar = nullptr;
     bool decode_kernel_ready = false;
 };
@@ -396,6 +399,10 @@ int32_t reserve(wq4_whisper *m, int64_t B)
         CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
         CHK(dev_alloc(m, &m->att_part, (size_t)n_cta * 4 * 68));   // [cta][kMaxSeg][68]
         CHK(dev_alloc(m, &m->arg_scratch, (size_t)n_cta * 8 * 2));
+        m->da_part_floats = B * (int64_t)m->cfg.n_text_head * 8 * 68;
+        CHK(dev_alloc(m, &m->da_part, (size_t)m->da_part_floats));
+        CHK(dev_alloc(m, &m->da_cnt, (size_t)(B * m->cfg.n_text_head)));
+        WQ4_CUDA(cudaMemset(m->da_cnt, 0, (size_t)(B * m->cfg.n_text_head) * sizeof(int)));
         CHK(dev_alloc(m, &m->grid_bar, 4));
         WQ4_CUDA(cudaDeviceSynchronize());
         m->decode_kernel_ready = true;
@@ -476,7 +483,15 @@ static bool use_decode_kernel()
 // kernel once per group, back to back on the stream: the caches are laid out [layer][B][..] so a group is a pointer
 // offset, and the kernel takes the layer stride (kv_clips) separately from its own batch.
 constexpr int64_t kDecodeGroup = 8;
-constexpr int64_t kDecodeGroupedMax = 24;     // beyond this the per-op path (weights read once per step) is faster
+// Largest batch that runs as groups of 8 through the single-kernel step.  Measured (profiles/r01_decode_step.txt): beyond
+// one group the per-op path, which reads the weights once per step and uses the split-KV attention kernel, is faster
+// (batch 16: 4.8 ms against 2 x 3.1 ms), so the default is a single group; WQ4_DECODE_GROUP_MAX overrides it (tests).
+static int64_t decode_grouped_max()
+{
+    static int64_t v = -1;
+    if (v < 0) { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); v = e ? atoll(e) : kDecodeGroup; if (v < 1) v = 1; }
+    return v;
+}
 
 int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
 {
@@ -505,7 +520,7 @@ int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv
 
 int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
 {
-    if (q_len == 1 && B <= kDecodeGroupedMax && m->decode_kernel_ready && use_decode_kernel() && m->dec.size() <= (size_t)kDecMaxLayers) {
+    if (q_len == 1 && B <= decode_grouped_max() && m->decode_kernel_ready && use_decode_kernel() && m->dec.size() <= (size_t)kDecMaxLayers) {
         if (kv_pos0 + 1 > m->cfg.n_text_ctx || emb_pos0 + 1 > m->cfg.n_text_ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
         return decode_step_fused(m, B, emb_pos0, kv_pos0, arg, st);
     }
@@ -521,13 +536,21 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         CHK(wq4m_layernorm(m->dx, L.attn_ln.w, L.attn_ln.b, m->dxn, nullptr, R, D, st));
         CHK(lin32(m, L.qkv, m->dxn, m->dqkv, nullptr, R, 0, st));
         CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
-        CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, q_len, kv_pos0 + q_len,
-                               q_len > 1 ? (int)kv_pos0 : -1, st));
+        if (q_len == 1 && m->da_part)
+            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, kv_pos0 + 1, m->da_part,
+                                         m->da_part_floats, m->da_cnt, m->device, st));
+        else
+            CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, q_len, kv_pos0 + q_len,
+                                   q_len > 1 ? (int)kv_pos0 : -1, st));
         CHK(lin32(m, L.out, m->datt, m->dx, m->dx, R, 0, st));
         // cross-attention over the cached encoder K/V (decoder.rs:95-104)
         CHK(wq4m_layernorm(m->dx, L.cross_ln.w, L.cross_ln.b, m->dxn, nullptr, R, D, st));
         CHK(lin32(m, L.cq, m->dxn, m->dq, nullptr, R, 0, st));
-        CHK(wq4m_dec_attention(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, q_len, m->T_enc, -1, st));
+        if (q_len == 1 && m->da_part)
+            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, m->T_enc, m->da_part,
+                                         m->da_part_floats, m->da_cnt, m->device, st));
+        else
+            CHK(wq4m_dec_attention(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, q_len, m->T_enc, -1, st));
         CHK(lin32(m, L.cout, m->datt, m->dx, m->dx, R, 0, st));
         // FFN (decoder.rs:107-110)
         CHK(wq4m_layernorm(m->dx, L.mlp_ln.w, L.mlp_ln.b, m->dxn, nullptr, R, D, st));
