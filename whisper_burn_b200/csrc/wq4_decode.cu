@@ -602,7 +602,8 @@ __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc,
 constexpr int kDaThreads = 256;
 __global__ void __launch_bounds__(kDaThreads)
 dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *__restrict__ kc, const __half *__restrict__ vc,
-                           long long ldkv, long long bstride, float *__restrict__ out, int ldo, int kv_len, int H, int nsplit,
+                           long long ldkv, long long bstride, float *__restrict__ out, __half *__restrict__ out16, int ldo, int kv_len,
+                           int H, int nsplit,
                            float *__restrict__ part, int *__restrict__ cnt)
 {
     __shared__ float sm[(kDaThreads / 32) * kPartStride];
@@ -700,10 +701,12 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
         o1 += sc * sm[w2 * kPartStride + 32 + lane];
     }
     float *orow = out + (size_t)b * ldo + h * 64;
+    __half *orow16 = out16 ? out16 + (size_t)b * ldo + h * 64 : nullptr;
     if (nsplit == 1) {
         const float inv = 1.0f / Lsum;
         orow[lane] = o0 * inv;
         orow[32 + lane] = o1 * inv;
+        if (orow16) { orow16[lane] = __float2half_rn(o0 * inv); orow16[32 + lane] = __float2half_rn(o1 * inv); }
         return;
     }
     float *pd = part + ((size_t)u * nsplit + sp) * kPartStride;
@@ -730,6 +733,7 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
     const float inv = 1.0f / Lg;
     orow[lane] = a0 * inv;
     orow[32 + lane] = a1 * inv;
+    if (orow16) { orow16[lane] = __float2half_rn(a0 * inv); orow16[32 + lane] = __float2half_rn(a1 * inv); }
     if (lane == 0) cnt[u] = 0;
 }
 
@@ -1115,11 +1119,12 @@ int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, i
     return WQ4_OK;
 }
 
-// q [B][ldq] f32, K/V f16 caches (row stride ldkv, clip stride kv_batch_stride elements), out [B][ldo] f32; one query row
+// q [B][ldq] f32, K/V f16 caches (row stride ldkv, clip stride kv_batch_stride elements), out [B][ldo] f32 (+ optional f16
+// copy out16 for the next GEMM); one query row
 // per clip.  part: >= B*H*nsplit*68 floats, cnt: >= B*H ints (zero; left zero).  nsplit is chosen here.
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
-                                 float *out, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part, int64_t part_floats,
-                                 int *cnt, int device, cudaStream_t st)
+                                 float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
+                                 int64_t part_floats, int *cnt, int device, cudaStream_t st)
 {
     const int64_t units = B * H;
     if (units < 1 || kv_len < 1) return WQ4_OK;
@@ -1131,8 +1136,8 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
     dim3 grid((unsigned)units, (unsigned)ns);
     dec_attention_split_kernel<<<grid, kDaThreads, 0, st>>>(q, (int)ldq, reinterpret_cast<const __half *>(kc),
                                                            reinterpret_cast<const __half *>(vc), (long long)ldkv,
-                                                           (long long)kv_batch_stride, out, (int)ldo, (int)kv_len, (int)H, (int)ns,
-                                                           part, cnt);
+                                                           (long long)kv_batch_stride, out, reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len,
+                                                           (int)H, (int)ns, part, cnt);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

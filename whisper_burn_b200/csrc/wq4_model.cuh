@@ -8,8 +8,8 @@ struct wq4_tensor;
 int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y32, void *y16, int64_t rows, int64_t D,
                        cudaStream_t st);
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
-                                 float *out, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part, int64_t part_floats,
-                                 int *cnt, int device, cudaStream_t st);
+                                 float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
+                                 int64_t part_floats, int *cnt, int device, cudaStream_t st);
 int32_t wq4m_enc_attention(const void *qkv16, void *out16, int64_t B, int64_t T, int64_t D, int64_t H, cudaStream_t st);
 // tcgen05 implementation (wq4_attn.cu); wq4m_enc_attention dispatches to it unless WQ4_ATTN_IMPL=1 (A/B runs).
 int32_t wq4m_enc_attention_tc(const void *qkv16, void *out16, int64_t B, int64_t T, int64_t D, int64_t H, cudaStream_t st);

@@ -157,6 +157,7 @@ struct wq4_whisper {
     __half *cross_kv = nullptr;      // [L][B*T_enc][2D]
     __half *self_k = nullptr, *self_v = nullptr;   // [L][B][n_text_ctx][D]
     float *dx = nullptr, *dxn = nullptr, *dqkv = nullptr, *datt = nullptr, *dq = nullptr, *dh = nullptr, *logits = nullptr;
+    __half *dxn16 = nullptr, *datt16 = nullptr, *dh16 = nullptr;   // f16 operands of the decoder GEMMs (rows > 8)
     int *d_tokens = nullptr, *d_next = nullptr, *d_sup_eot = nullptr, *d_sup_none = nullptr;
     int *h_next = nullptr;           // pinned
     void *lin_ws = nullptr;
@@ -365,6 +366,9 @@ int32_t reserve(wq4_whisper *m, int64_t B)
     CHK(dev_alloc(m, &m->datt, (size_t)R * D));
     CHK(dev_alloc(m, &m->dq, (size_t)R * D));
     CHK(dev_alloc(m, &m->dh, (size_t)R * F));
+    CHK(dev_alloc(m, &m->dxn16, (size_t)R * D));
+    CHK(dev_alloc(m, &m->datt16, (size_t)R * D));
+    CHK(dev_alloc(m, &m->dh16, (size_t)R * F));
     CHK(dev_alloc(m, &m->logits, (size_t)B * m->V));
     CHK(dev_alloc(m, &m->d_tokens, (size_t)R));
     CHK(dev_alloc(m, &m->d_next, (size_t)B));
@@ -532,30 +536,45 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         DecLayer &L = m->dec[l];
         __half *sk = m->self_k + l * (size_t)B * ctx * D, *sv = m->self_v + l * (size_t)B * ctx * D;
         const __half *ck = m->cross_kv + l * (size_t)M * 2 * D;
+        // Rows > 8 run on the tensor-core GEMM, whose operand is f16: the producers (LayerNorm, split attention, fc1's
+        // epilogue) emit it directly; rows <= 8 use the f32 GEMV.  (f16p = single-query step on the GEMM path.)
+        const bool g16 = R > 8, f16p = g16 && q_len == 1 && m->da_part;
+        auto ln = [&](const LNp &w) { return wq4m_layernorm(m->dx, w.w, w.b, g16 ? nullptr : m->dxn, g16 ? m->dxn16 : nullptr, R, D, st); };
+        auto lin_n = [&](const Lin &l, float *y32, void *y16, uint32_t flags) {       // input: the LayerNorm output
+            return g16 ? lin16(l, m->dxn16, y32, y16, nullptr, R, flags, st) : lin32(m, l, m->dxn, y32, nullptr, R, flags, st);
+        };
+        auto lin_att = [&](const Lin &l) {                                             // input: attention output, + residual
+            return f16p ? lin16(l, m->datt16, m->dx, nullptr, m->dx, R, 0, st) : lin32(m, l, m->datt, m->dx, m->dx, R, 0, st);
+        };
         // self-attention with cache (decoder.rs:84-92 / 147-152)
-        CHK(wq4m_layernorm(m->dx, L.attn_ln.w, L.attn_ln.b, m->dxn, nullptr, R, D, st));
-        CHK(lin32(m, L.qkv, m->dxn, m->dqkv, nullptr, R, 0, st));
+        CHK(ln(L.attn_ln));
+        CHK(lin_n(L.qkv, m->dqkv, nullptr, 0));
         CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
         if (q_len == 1 && m->da_part)
-            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, kv_pos0 + 1, m->da_part,
-                                         m->da_part_floats, m->da_cnt, m->device, st));
+            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, f16p ? m->datt16 : nullptr, D, B, H, kv_pos0 + 1,
+                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
         else
             CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, q_len, kv_pos0 + q_len,
                                    q_len > 1 ? (int)kv_pos0 : -1, st));
-        CHK(lin32(m, L.out, m->datt, m->dx, m->dx, R, 0, st));
+        CHK(lin_att(L.out));
         // cross-attention over the cached encoder K/V (decoder.rs:95-104)
-        CHK(wq4m_layernorm(m->dx, L.cross_ln.w, L.cross_ln.b, m->dxn, nullptr, R, D, st));
-        CHK(lin32(m, L.cq, m->dxn, m->dq, nullptr, R, 0, st));
+        CHK(ln(L.cross_ln));
+        CHK(lin_n(L.cq, m->dq, nullptr, 0));
         if (q_len == 1 && m->da_part)
-            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, m->T_enc, m->da_part,
-                                         m->da_part_floats, m->da_cnt, m->device, st));
+            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, f16p ? m->datt16 : nullptr, D, B, H,
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
         else
             CHK(wq4m_dec_attention(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, q_len, m->T_enc, -1, st));
-        CHK(lin32(m, L.cout, m->datt, m->dx, m->dx, R, 0, st));
+        CHK(lin_att(L.cout));
         // FFN (decoder.rs:107-110)
-        CHK(wq4m_layernorm(m->dx, L.mlp_ln.w, L.mlp_ln.b, m->dxn, nullptr, R, D, st));
-        CHK(lin32(m, L.fc1, m->dxn, m->dh, nullptr, R, WQ4_EPI_GELU, st));
-        CHK(lin32(m, L.fc2, m->dh, m->dx, m->dx, R, 0, st));
+        CHK(ln(L.mlp_ln));
+        if (g16) {
+            CHK(lin16(L.fc1, m->dxn16, nullptr, m->dh16, nullptr, R, WQ4_EPI_GELU, st));
+            CHK(lin16(L.fc2, m->dh16, m->dx, nullptr, m->dx, R, 0, st));
+        } else {
+            CHK(lin32(m, L.fc1, m->dxn, m->dh, nullptr, R, WQ4_EPI_GELU, st));
+            CHK(lin32(m, L.fc2, m->dh, m->dx, m->dx, R, 0, st));
+        }
     }
     // final LN on the last position of every clip, then logits = x . token_embedding^T (decoder.rs:286-292)
     if (q_len == 1) {
