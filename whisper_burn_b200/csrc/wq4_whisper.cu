@@ -166,6 +166,8 @@ struct wq4_whisper {
     // decode-step megakernel state (wq4_decode.cu): decode-layout copies of the decoder linears, f16 logits matrix
     std::vector<DecLayerW> dec_w_host;
     uint4 *tok_emb16t = nullptr;     // [D/8][Vp] f16 chunks
+    __half *tok_emb16 = nullptr;     // [Vp256][D] f16 rows, zero padded: the dense-GEMM logits of batches above one decode group
+    int64_t Vp256 = 0;
     int64_t Vp = 0;
     float *att_part = nullptr, *arg_scratch = nullptr;
     float *da_part = nullptr;      // split-KV partials of the per-op decode attention: [B*H][8][68]
@@ -401,6 +403,12 @@ int32_t reserve(wq4_whisper *m, int64_t B)
         m->Vp = (m->V + 31) / 32 * 32;
         CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
         CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
+        if (B > 8) {   // batches that can exceed one decode group take the per-op path
+            m->Vp256 = (m->V + 255) / 256 * 256;
+            CHK(dev_alloc(m, &m->tok_emb16, (size_t)m->Vp256 * D));
+            WQ4_CUDA(cudaMemset(m->tok_emb16, 0, (size_t)m->Vp256 * D * 2));
+            CHK(wq4_launch_cvt_f32_to_16(m->tok_emb, m->tok_emb16, m->V * D, false, nullptr));
+        }
         CHK(dev_alloc(m, &m->att_part, (size_t)n_cta * 4 * 68));   // [cta][kMaxSeg][68]
         CHK(dev_alloc(m, &m->arg_scratch, (size_t)n_cta * 8 * 2));
         m->da_part_floats = B * (int64_t)m->cfg.n_text_head * 8 * 68;
@@ -577,16 +585,35 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         }
     }
     // final LN on the last position of every clip, then logits = x . token_embedding^T (decoder.rs:286-292)
-    if (q_len == 1) {
-        CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, B, D, st));
+    if (R > 8 && m->tok_emb16) {
+        // batches above one decode group: the logits are one tensor-core GEMM on the f16 embedding rows
+        const void *last16 = m->dxn16;
+        if (q_len == 1) {
+            CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, nullptr, m->dxn16, B, D, st));
+        } else {
+            CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, nullptr, m->dxn16, R, D, st));
+            WQ4_CUDA(cudaMemcpy2DAsync(m->datt16, D * 2, m->dxn16 + (q_len - 1) * D, q_len * D * 2, D * 2, B, cudaMemcpyDeviceToDevice, st));
+            last16 = m->datt16;
+        }
+        DenseGemmArgs ga = {};
+        ga.w16 = m->tok_emb16; ga.x16 = last16; ga.y_f32 = m->logits;
+        ga.n = m->V; ga.n_pad = m->Vp256; ga.kdim_pad = D;
+        ga.x_k = D; ga.x_rows = B; ga.x_batch = 1; ga.x_row_stride = D; ga.x_batch_stride = B * D;
+        ga.ob = B * m->V; ga.ot = m->V; ga.on = 1;
+        ga.device = m->device; ga.stream = st;
+        CHK(wq4_launch_gemm_dense(ga, B <= 32 ? 32 : 64));
     } else {
-        CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, R, D, st));
-        // gather last rows: dxn[b*q_len + q_len-1] -> dq[b]
-        WQ4_CUDA(cudaMemcpy2DAsync(m->dq, D * 4, m->dxn + (q_len - 1) * D, q_len * D * 4, D * 4, B, cudaMemcpyDeviceToDevice, st));
+        if (q_len == 1) {
+            CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, B, D, st));
+        } else {
+            CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, R, D, st));
+            // gather last rows: dxn[b*q_len + q_len-1] -> dq[b]
+            WQ4_CUDA(cudaMemcpy2DAsync(m->dq, D * 4, m->dxn + (q_len - 1) * D, q_len * D * 4, D * 4, B, cudaMemcpyDeviceToDevice, st));
+        }
+        const float *last = q_len == 1 ? m->dxn : m->dq;
+        CHK(wq4m_logits(last, m->tok_emb, m->logits, B, D, m->V, st));
     }
-    const float *last = q_len == 1 ? m->dxn : m->dq;
     (void)F;
-    CHK(wq4m_logits(last, m->tok_emb, m->logits, B, D, m->V, st));
     if (arg && arg->hi > arg->lo) CHK(wq4m_argmax(m->logits, B, m->V, arg->lo, arg->hi, arg->suppress, arg->out, st));
     return WQ4_OK;
 }
