@@ -10,7 +10,7 @@ fn main() {
     let out = PathBuf::from(env::var("OUT_DIR").unwrap());
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
     let lib = out.join("libwq4.so");
-    let sources = ["wq4_api.cu", "wq4_tensor.cu", "wq4_gemv.cu", "wq4_gemm.cu", "wq4_gemm2.cu", "wq4_model_kernels.cu", "wq4_decode.cu", "wq4_attn.cu", "wq4_mel.cu", "wq4_whisper.cu"];
+    let sources = ["wq4_api.cu", "wq4_tensor.cu", "wq4_gemv.cu", "wq4_skinny.cu", "wq4_gemm.cu", "wq4_gemm2.cu", "wq4_model_kernels.cu", "wq4_decode.cu", "wq4_attn.cu", "wq4_mel.cu", "wq4_whisper.cu"];
     let mut cmd = Command::new(&nvcc);
     cmd.args([
         "-arch=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-shared", "-cudart", "static",

@@ -40,6 +40,7 @@ pub const WQ4_EPI_GELU: u32 = 1;
 pub const WQ4_OPERANDS_BF16: u32 = 16;
 pub const WQ4_FORCE_GEMM: u32 = 32;
 pub const WQ4_FORCE_GEMV: u32 = 64;
+pub const WQ4_FORCE_SKINNY: u32 = 128;
 
 extern "C" {
     pub fn wq4_last_error() -> *const c_char;

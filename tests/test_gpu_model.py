@@ -189,3 +189,19 @@ def test_grouped_decode_kernel_in_child_process():
                         "every_batch_size and (11 or 19)"], env=env, capture_output=True, text=True, timeout=900)
     print(r.stdout[-600:], r.stderr[-600:])
     assert r.returncode == 0 and "2 passed" in r.stdout
+
+
+def test_per_op_decode_without_skinny_kernel_in_child_process():
+    """WQ4_SKINNY=0 (read once per process) keeps the previous per-op decode path -- separate LayerNorm and cache-append
+    launches, tcgen05 GEMM at 9..64 rows -- as the A/B arm of the skinny linear; batches 11 and 26 against the oracle."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    if os.environ.get("WQ4_SKINNY") or os.environ.get("WQ4_DECODE_GROUP_MAX"):
+        pytest.skip("already inside a child")
+    env = dict(os.environ, WQ4_SKINNY="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-q", "-x", "-m", "gpu", "-k",
+                        "every_batch_size and (11 or 26)"], env=env, capture_output=True, text=True, timeout=900)
+    print(r.stdout[-600:], r.stderr[-600:])
+    assert r.returncode == 0 and "2 passed" in r.stdout

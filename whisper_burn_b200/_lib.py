@@ -17,6 +17,7 @@ WQ4_EPI_GELU = 1
 WQ4_OPERANDS_BF16 = 16
 WQ4_FORCE_GEMM = 32
 WQ4_FORCE_GEMV = 64
+WQ4_FORCE_SKINNY = 128
 
 _STATUS = {1: "invalid argument", 2: "shape", 3: "byte count", 4: "cuda", 5: "unsupported", 6: "workspace"}
 

@@ -432,6 +432,23 @@ int32_t lin32(wq4_whisper *m, const Lin &l, const float *x, float *y, const floa
     return wq4_linear_forward_ex(l.w, l.bias, x, nullptr, y, nullptr, res, rows, flags, m->lin_ws, m->lin_ws_bytes, st);
 }
 
+// Skinny linear (wq4_skinny.cu) with its optional extras: LayerNorm fused on load, K/V append.
+int32_t lin_sk(const Lin &l, const float *x32, const void *x16, const LNp *ln, float *y32, void *y16, const float *res, int64_t rows,
+               uint32_t flags, SkinnyExtra ex, cudaStream_t st)
+{
+    LinearArgs a = {};
+    a.w = l.w; a.bias = l.bias; a.x_f32 = x32; a.x_f16 = x16; a.y_f32 = y32; a.y_f16 = y16; a.residual = res;
+    a.rows = rows; a.flags = flags; a.stream = st;
+    if (ln) { ex.ln_w = ln->w; ex.ln_b = ln->b; }
+    return wq4_launch_skinny(a, &ex);
+}
+static bool use_skinny_step()
+{
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("WQ4_SKINNY"); v = (e && atoi(e) == 0) ? 0 : 1; }   // 0 = tcgen05 GEMM + separate LN / append (A/B runs)
+    return v == 1;
+}
+
 // WhisperEncoder::forward (encoder.rs:87-115) for B clips; mel_dev [B, n_mels, 3000] f32.
 int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
 {
@@ -554,6 +571,24 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         auto lin_att = [&](const Lin &l) {                                             // input: attention output, + residual
             return f16p ? lin16(l, m->datt16, m->dx, nullptr, m->dx, R, 0, st) : lin32(m, l, m->datt, m->dx, m->dx, R, 0, st);
         };
+        if (f16p && R <= WQ4_SKINNY_MAX_ROWS && use_skinny_step()) {
+            // Single-query step of 9..64 clips: eight launches per layer.  The skinny linear applies LayerNorm on load
+            // (q|k|v, cross-q, fc1), appends the new K/V rows to the f16 cache from the q|k|v epilogue and adds the
+            // residual in place; the split-KV attention emits the f16 operand of the following projection.
+            SkinnyExtra none = {}, kv = {};
+            kv.kc = sk; kv.vc = sv; kv.kv_batch_stride = ctx * D; kv.kv_ld = D; kv.kv_pos = kv_pos0; kv.kv_d = D;
+            CHK(lin_sk(L.qkv, m->dx, nullptr, &L.attn_ln, m->dqkv, nullptr, nullptr, R, 0, kv, st));
+            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, m->datt16, D, B, H, kv_pos0 + 1,
+                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
+            CHK(lin_sk(L.out, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
+            CHK(lin_sk(L.cq, m->dx, nullptr, &L.cross_ln, m->dq, nullptr, nullptr, R, 0, none, st));
+            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, m->datt16, D, B, H,
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
+            CHK(lin_sk(L.cout, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
+            CHK(lin_sk(L.fc1, m->dx, nullptr, &L.mlp_ln, nullptr, m->dh16, nullptr, R, WQ4_EPI_GELU, none, st));
+            CHK(lin_sk(L.fc2, nullptr, m->dh16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
+            continue;
+        }
         // self-attention with cache (decoder.rs:84-92 / 147-152)
         CHK(ln(L.attn_ln));
         CHK(lin_n(L.qkv, m->dqkv, nullptr, 0));
