@@ -66,7 +66,7 @@ enum {
     WQ4_OPERANDS_BF16 = 16,  /* tensor-core operands in bf16 instead of the default f16    */
     WQ4_FORCE_GEMM = 32,     /* use the tcgen05 GEMM kernel even for tiny M                */
     WQ4_FORCE_GEMV = 64,     /* use the CUDA-core GEMV kernel (M <= 8 only)                */
-    WQ4_FORCE_SKINNY = 128   /* use the mma.sync skinny kernel (M <= 64 only; default 9..64) */
+    WQ4_FORCE_SKINNY = 128   /* use the mma.sync skinny kernel (M <= 64 only; default 9..16) */
 };
 
 WQ4_API const char *wq4_last_error(void);
@@ -197,7 +197,7 @@ WQ4_API int32_t wq4_logmel_forward(const wq4_logmel *m, const float *pcm_dev, in
 
 /* ---- Introspection used by bench.py / tests ------------------------------------------- */
 /* Which kernel family a [rows,K]x[N,K]^T call dispatches to: 0 = GEMV (CUDA cores),
- * 1 = tcgen05 GEMM, 2 = mma.sync skinny kernel (9..64 rows).  `tile_m` receives the GEMM row tile
+ * 1 = tcgen05 GEMM, 2 = mma.sync skinny kernel (9..16 rows, or forced).  `tile_m` receives the GEMM row tile
  * (0 for GEMV, 16 = weight rows per CTA for the skinny kernel). */
 WQ4_API int32_t wq4_linear_plan(const wq4_tensor *w, int64_t rows, uint32_t flags,
                                 int32_t *tile_m);

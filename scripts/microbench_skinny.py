@@ -36,12 +36,15 @@ if __name__ == "__main__":
     peak = 6455.0
     print("rows  N     K     kernel            us      GB/s (Q4 bytes + x + y)")
     for n, k in ((1280, 1280), (3840, 1280), (5120, 1280), (1280, 5120)):
-        for rows in (4, 8, 16, 32, 64):
+        for rows in ([int(v) for v in sys.argv[1].split(',')] if len(sys.argv) > 1 else (4, 8, 16, 32, 64)):
             byts = n * k // 32 * 18 + rows * k * 2 + rows * n * 4 + n * 4
-            arms = [("skinny f16x", wb.WQ4_FORCE_SKINNY, "f16"), ("skinny f32x", wb.WQ4_FORCE_SKINNY, "f32"),
-                    ("tcgen05 gemm", wb.WQ4_FORCE_GEMM, "f16")]
+            arms = [("skinny f16x", wb.WQ4_FORCE_SKINNY, "f16"), ("tcgen05 gemm", wb.WQ4_FORCE_GEMM, "f16")]
             if rows <= 8:
                 arms.append(("gemv f32", wb.WQ4_FORCE_GEMV, "f32"))
+            else:
+                arms.append(("skinny f32x", wb.WQ4_FORCE_SKINNY, "f32"))
+            if len(sys.argv) > 2:
+                arms = arms[:1]
             for name, fl, xk in arms:
                 dt = run_one(rows, n, k, fl, xk)
                 print(f"{rows:4d} {n:5d} {k:5d}  {name:14s} {dt * 1e6:8.2f}  {byts / dt / 1e9:8.1f}  ({100 * byts / dt / 1e9 / peak:4.1f}% of {peak:.0f})", flush=True)

@@ -1,7 +1,7 @@
 """The skinny Q4 linear (csrc/wq4_skinny.cu: 1..64 activation rows, mma.sync with the weight rows as the MMA M dimension)
 through the C ABI, every row-tile count, both activation types and every epilogue mode, against the f64 product of the
 oracle's dequantised weights (oracle/q4.py, tensor.rs:96-109 twin) with the f16-rounded activations; tolerance 1e-3 of the
-output scale (src/gguf/tests.rs:406).  Also: default dispatch for 9..64 rows, and run-to-run determinism."""
+output scale (src/gguf/tests.rs:406).  Also: default dispatch for 9..16 rows, and run-to-run determinism."""
 import ctypes as C
 
 import numpy as np
@@ -23,8 +23,9 @@ def _p(a):
 
 
 def _call(t, bias, x32, x16, y32, y16, res, rows, flags):
+    ws = torch.empty(rows * t.shape()[1] * 2 + 256, dtype=torch.uint8, device=DEV)     # f16 copy of an f32 x
     wb._lib.check(wb.lib().wq4_linear_forward_ex(t._h, _p(bias), _p(x32), _p(x16), _p(y32), _p(y16), _p(res), rows, flags,
-                                                 None, 0, C.c_void_p(_stream(DEV))))
+                                                 _p(ws), ws.numel(), C.c_void_p(_stream(DEV))))
     torch.cuda.synchronize()
     assert wb.lib().wq4_device_error_flag(0) == 0
 
@@ -79,10 +80,12 @@ def test_default_dispatch_and_determinism():
     tile = C.c_int32()
     assert L.wq4_linear_plan(t._h, 8, 0, C.byref(tile)) == 0
     assert L.wq4_linear_plan(t._h, 9, 0, C.byref(tile)) == 2 and tile.value == 16
-    assert L.wq4_linear_plan(t._h, 64, 0, C.byref(tile)) == 2
-    assert L.wq4_linear_plan(t._h, 65, 0, C.byref(tile)) == 1
-    assert L.wq4_linear_plan(t._h, 32, wb.WQ4_FORCE_GEMM, C.byref(tile)) == 1
-    x = torch.from_numpy(rng.standard_normal((1, 32, k)).astype(np.float32)).to(DEV)
+    assert L.wq4_linear_plan(t._h, 16, 0, C.byref(tile)) == 2
+    assert L.wq4_linear_plan(t._h, 17, 0, C.byref(tile)) == 1          # beyond 16 rows the tcgen05 GEMM is faster
+    assert L.wq4_linear_plan(t._h, 64, wb.WQ4_FORCE_SKINNY, C.byref(tile)) == 2
+    assert L.wq4_linear_plan(t._h, 65, wb.WQ4_FORCE_SKINNY, C.byref(tile)) == 1
+    assert L.wq4_linear_plan(t._h, 12, wb.WQ4_FORCE_GEMM, C.byref(tile)) == 1
+    x = torch.from_numpy(rng.standard_normal((1, 14, k)).astype(np.float32)).to(DEV)
     bias = torch.from_numpy(rng.standard_normal(n).astype(np.float32)).to(DEV)
     lin = wb.Q4Linear(t, bias)
     a = lin.forward(x)

@@ -203,16 +203,17 @@ static bool use_gemv(int64_t rows, uint32_t flags, bool has_f32_x)
     return rows <= 8;
 }
 
-// 9..64 rows: the mma.sync skinny kernel (16 weight rows per CTA) instead of 256-row tcgen05 tiles on a handful of SMs.
+// 9..16 rows (up to 64 with WQ4_FORCE_SKINNY): the mma.sync skinny kernel (16 weight rows per CTA) instead of 256-row
+// tcgen05 tiles on a handful of SMs; beyond 16 rows the tcgen05 kernel is the faster one (wq4_skinny.cu header).
 // WQ4_SKINNY=0 in the environment restores the tcgen05 path for these row counts (A/B runs).
-static bool use_skinny(int64_t rows, uint32_t flags)
+static bool use_skinny(const wq4_tensor *w, int64_t rows, uint32_t flags)
 {
     static int on = -1;
     if (on < 0) { const char *e = getenv("WQ4_SKINNY"); on = (e && atoi(e) == 0) ? 0 : 1; }
     if (flags & (WQ4_FORCE_GEMM | WQ4_OPERANDS_BF16)) return false;
-    if (rows > WQ4_SKINNY_MAX_ROWS) return false;
+    if (!wq4_skinny_supported(w, rows)) return false;
     if (flags & WQ4_FORCE_SKINNY) return true;
-    return on && rows > 8;
+    return on && rows > 8 && rows <= WQ4_SKINNY_DEFAULT_ROWS;
 }
 
 static int32_t check_linear(const wq4_tensor *w, const char *who)
@@ -290,7 +291,7 @@ int32_t wq4_linear_plan(const wq4_tensor *w, int64_t rows, uint32_t flags, int32
         if (tile_m) *tile_m = 0;
         return 0;
     }
-    if (use_skinny(rows, flags)) {
+    if (use_skinny(w, rows, flags)) {
         if (tile_m) *tile_m = 16;      /* weight rows per CTA of the skinny kernel */
         return 2;
     }
@@ -327,7 +328,7 @@ int32_t wq4_linear_forward_ex(const wq4_tensor *w, const float *bias_dev, const 
     bool gemv = use_gemv(rows, flags, x_f32_dev != nullptr);
     if ((flags & WQ4_FORCE_GEMV) && rows <= 8 && x_f32_dev) gemv = true;
     if (gemv) return wq4_launch_gemv(a);
-    if (use_skinny(rows, flags)) return wq4_launch_skinny(a, nullptr);
+    if (use_skinny(w, rows, flags)) return wq4_launch_skinny(a, nullptr);
     if (wq4_gemm_impl() == 2) return wq4_launch_gemm2_q4(a, wq4_pick_tile_m2(rows, w->np_alloc / 2));
     return wq4_launch_gemm_q4(a, wq4_pick_tile_m(rows, w->np));
 }

@@ -116,15 +116,18 @@ struct LinearArgs {
 
 int32_t wq4_launch_gemv(const LinearArgs &a);
 int32_t wq4_launch_gemm_q4(const LinearArgs &a, int tile_m);
-// Skinny linear (wq4_skinny.cu): 1..64 activation rows on mma.sync, 16 weight rows per CTA.  Optional extras: LayerNorm fused
-// on load (f32 x only) and the K/V thirds of a fused q|k|v projection appended to the f16 self-attention cache.
+// Skinny linear (wq4_skinny.cu): 1..64 activation rows on mma.sync, 16 weight rows per CTA (default dispatch: 9..16 rows).
+// Optional extras: LayerNorm fused on load (f32 x only) and the K/V thirds of a fused q|k|v projection appended to the f16
+// self-attention cache.
 #define WQ4_SKINNY_MAX_ROWS 64
+#define WQ4_SKINNY_DEFAULT_ROWS 16
 struct SkinnyExtra {
     const float *ln_w, *ln_b;          // LayerNorm weight / bias over K, or null
     void *kc, *vc;                     // f16 caches [clip][ctx][kv_ld] or null; row m of x belongs to clip m
     int64_t kv_batch_stride, kv_ld, kv_pos, kv_d;
 };
 int32_t wq4_launch_skinny(const LinearArgs &a, const SkinnyExtra *ex);
+bool wq4_skinny_supported(const wq4_tensor *w, int64_t rows);   // matrix-mode weight, 1..64 rows
 int wq4_pick_tile_m(int64_t rows, int64_t np);
 // second-generation Q4 GEMM (CTA pair, A operand in tensor memory; wq4_gemm2.cu)
 int32_t wq4_launch_gemm2_q4(const LinearArgs &a, int tile_m);

@@ -26,6 +26,7 @@
 
 #include "wq4_common.cuh"
 #include "wq4_model.cuh"
+#include "wq4_ptx.cuh"
 
 namespace {
 
@@ -482,7 +483,7 @@ __device__ __forceinline__ AttnPlan attn_plan(int units, int kv, int grid)
 
 template <bool kFreshKV>
 __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc, const __half *vc, long long ldkv,
-                                        long long bstride, int kv_len, int B, int H, AttnPlan pl, float *part, float *sm)
+                                        long long bstride, long long hstride, int kv_len, int B, int H, AttnPlan pl, float *part, float *sm)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 3, dch = lane & 7;
@@ -506,8 +507,8 @@ __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc,
             qv[0] = a.x * 0.125f; qv[1] = a.y * 0.125f; qv[2] = a.z * 0.125f; qv[3] = a.w * 0.125f;
             qv[4] = c.x * 0.125f; qv[5] = c.y * 0.125f; qv[6] = c.z * 0.125f; qv[7] = c.w * 0.125f;
         }
-        const __half *kb_ = kc + (size_t)b * bstride + h * 64 + dch * 8;
-        const __half *vb_ = vc + (size_t)b * bstride + h * 64 + dch * 8;
+        const __half *kb_ = kc + (size_t)b * bstride + (size_t)h * hstride + dch * 8;
+        const __half *vb_ = vc + (size_t)b * bstride + (size_t)h * hstride + dch * 8;
         Soft st;
         st.m = -INFINITY; st.l = 0.0f;
 #pragma unroll
@@ -599,101 +600,192 @@ __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc,
 // One query row per clip, f16 KV cache, non-causal: grid (clip*head, split).  Same inner loop as attn_phase (8 lanes per
 // 128-byte key row, 4 keys per lane group in flight, online softmax); with more than one split per unit the last CTA to
 // finish a unit merges its partials ("fix-up" by an arrival counter that it resets), so there is no second launch.
-constexpr int kDaThreads = 256;
-__global__ void __launch_bounds__(kDaThreads)
+// sm_100 mixed-precision FMA (PTX fma.rn.f32.f16, SASS FHFMA): acc += a.h * b.h with f16 operands taken as register halves.
+__device__ __forceinline__ void fhfma_pair(float &acc_lo, float &acc_hi, uint32_t a2, uint32_t b2)      // (a.lo*b.lo, a.hi*b.hi)
+{
+    asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %2;\n\tmov.b32 {bl, bh}, %3;\n\t"
+        "fma.rn.f32.f16 %0, al, bl, %0;\n\tfma.rn.f32.f16 %1, ah, bh, %1;\n\t}"
+        : "+f"(acc_lo), "+f"(acc_hi) : "r"(a2), "r"(b2));
+}
+__device__ __forceinline__ void fhfma_scalar(float &acc_lo, float &acc_hi, uint32_t a2, unsigned short s)   // (a.lo*s, a.hi*s)
+{
+    asm("{\n\t.reg .b16 al, ah;\n\tmov.b32 {al, ah}, %2;\n\t"
+        "fma.rn.f32.f16 %0, al, %3, %0;\n\tfma.rn.f32.f16 %1, ah, %3, %1;\n\t}"
+        : "+f"(acc_lo), "+f"(acc_hi) : "r"(a2), "h"(s));
+}
+
+constexpr int kDaStages = 3;
+constexpr size_t da_smem(int warps) { return (size_t)warps * kDaStages * 2 * 32 * 128; }   // warp-private rings: 24 KB per warp
+// kDaW warps per CTA: 8 for long key ranges (cross-attention: 192 KB of ring, one CTA per SM, 128 KB in flight), 2 for
+// short ones (self-attention over <= 448 keys: 48 KB, four CTAs per SM, so that a 640-unit launch is about one wave).
+template <int kDaW>
+__global__ void __launch_bounds__(kDaW * 32, kDaW == 8 ? 1 : 4)
 dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *__restrict__ kc, const __half *__restrict__ vc,
-                           long long ldkv, long long bstride, float *__restrict__ out, __half *__restrict__ out16, int ldo, int kv_len,
+                           long long ldkv, long long bstride, long long hstride, float *__restrict__ out, __half *__restrict__ out16, int ldo, int kv_len,
                            int H, int nsplit,
                            float *__restrict__ part, int *__restrict__ cnt)
 {
-    __shared__ float sm[(kDaThreads / 32) * kPartStride];
+    __shared__ float sm[(kDaW) * kPartStride];
     __shared__ int s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int g = lane >> 3, dch = lane & 7;
     const int u = blockIdx.x, sp = blockIdx.y, h = u % H, b = u / H;
     const int per = (kv_len + nsplit - 1) / nsplit;
     const int k0 = sp * per, k1 = min(kv_len, k0 + per);
-    float qv[8];
+    ptx::grid_dep_launch();     // PDL: the following projection may be scheduled and prefetch its weights
+    ptx::grid_dep_wait();       // q and the new K/V row come from the previous kernel
+
+    // ONE KEY PER LANE.  The first form of this kernel spread a key over 8 lanes (8 dims each): three shuffles, two
+    // exponentials and the loop overhead per key quad made it issue bound -- 24 M warp instructions, 52 % issue-active with
+    // 16 resident warps, 54 us for the 246 MB cross-attention read of a 32-clip step (4.5 TB/s; ncu profiles/r01).  Here a lane
+    // owns a whole 64-dim key row: no shuffles in the loop, one exponential per key, 64 independent accumulators of ILP, and
+    // a single butterfly reduce-scatter over the warp at the end.  Rows are staged by cp.async into a warp-private ring
+    // (kDaStages x 32 keys x (128 B K + 128 B V)), copied as coalesced 16-byte chunks and swizzled (chunk ^ key&7) so that
+    // the row-per-lane reads are bank-conflict free.
+    extern __shared__ __align__(128) uint8_t da_ring[];    // [warp][stage][K|V][32 keys][128 B]
+    constexpr uint32_t kHalf = 32 * 128, kStage = 2 * kHalf, kWarpRing = kDaStages * kStage;
+    const uint32_t ring = ptx::smem_u32(da_ring) + (uint32_t)warp * kWarpRing;
+    const uint8_t *ring_p = da_ring + (size_t)warp * kWarpRing;
+    const __half *kb_ = kc + (size_t)b * bstride + (size_t)h * hstride;
+    const __half *vb_ = vc + (size_t)b * bstride + (size_t)h * hstride;
+    const int nblocks = (k1 - k0 + 31) >> 5;                                   // 32-key blocks of this CTA's range
+    const int n_it = nblocks > warp ? (nblocks - warp + kDaW - 1) / (kDaW) : 0;   // blocks warp, warp+8, ...
+    // chunk id = i*32 + lane of a 32-key block: key kl = 4i + (lane >> 3), 16-byte chunk c = lane & 7 (8 lanes = one 128-byte
+    // row: coalesced); swizzled slot (c ^ (kl & 7)) with kl & 7 = 4*(i & 1) + (lane >> 3).  All per-lane parts are hoisted.
+    const int kl0 = lane >> 3, cch = lane & 7;
+    const char *gk0 = reinterpret_cast<const char *>(kb_ + (size_t)(k0 + warp * 32 + kl0) * ldkv + cch * 8);
+    const char *gv0 = reinterpret_cast<const char *>(vb_ + (size_t)(k0 + warp * 32 + kl0) * ldkv + cch * 8);
+    const size_t step_i = (size_t)ldkv * 8, step_it = (size_t)ldkv * (kDaW) * 64;      // bytes: 4 keys / 256 keys
+    const uint32_t sw_even = (uint32_t)(kl0 * 128 + ((cch ^ kl0) << 4)), sw_odd = (uint32_t)(kl0 * 128 + ((cch ^ (4 | kl0)) << 4));
+    auto issue = [&](int it) {
+        if (it < n_it) {
+            const int rem = k1 - (k0 + (warp + it * (kDaW)) * 32) - kl0;     // key 4i + kl0 of the block is valid iff 4i < rem
+            const uint32_t dst = ring + (uint32_t)(it % kDaStages) * kStage;
+            const char *gk = gk0 + (size_t)it * step_it, *gv = gv0 + (size_t)it * step_it;
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (4 * i < rem) {
+                    const uint32_t d = dst + (uint32_t)(i * 512) + ((i & 1) ? sw_odd : sw_even);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gk + i * step_i) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + kHalf), "l"(gv + i * step_i) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int s2 = 0; s2 < kDaStages - 1; s2++) issue(s2);
+
+    // q as packed f16 pairs: the products run on the mixed-precision FMA of sm_100 (fma.rn.f32.f16 -> FHFMA: f16 x f16 + f32,
+    // operand halves addressed in place), which removes the 128 half->float conversions per key that made up a fifth of
+    // the instruction stream.  q is rounded to f16 like every tensor-core operand of this library; the
+    // product and the accumulation are exact / f32.
+    uint32_t qh[32];
     {
-        const float *qp = q + (size_t)b * ldq + h * 64 + dch * 8;
-        const float4 a = *reinterpret_cast<const float4 *>(qp);
-        const float4 c = *(reinterpret_cast<const float4 *>(qp) + 1);
-        qv[0] = a.x * 0.125f; qv[1] = a.y * 0.125f; qv[2] = a.z * 0.125f; qv[3] = a.w * 0.125f;
-        qv[4] = c.x * 0.125f; qv[5] = c.y * 0.125f; qv[6] = c.z * 0.125f; qv[7] = c.w * 0.125f;
-    }
-    const __half *kb_ = kc + (size_t)b * bstride + h * 64 + dch * 8;
-    const __half *vb_ = vc + (size_t)b * bstride + h * 64 + dch * 8;
-    Soft st;
-    st.m = -INFINITY; st.l = 0.0f;
+        const float4 *qp = reinterpret_cast<const float4 *>(q + (size_t)b * ldq + h * 64);
 #pragma unroll
-    for (int j = 0; j < 8; j++) st.o[j] = 0.0f;
-    constexpr int NT = 4, KW = kDaThreads / 32 * 4;        // keys per t-step over the CTA
-    for (int base0 = k0 + warp * 4; base0 < k1; base0 += KW * NT) {      // warp-uniform trip count (shuffles inside)
-        const int key0 = base0 + g;
-        uint4 kq[NT], vq[NT];
-        bool ok[NT];
-#pragma unroll
-        for (int t = 0; t < NT; t++) {
-            const int key = key0 + t * KW;
-            ok[t] = key < k1;
-            if (ok[t]) {
-                kq[t] = ldg_stream16(reinterpret_cast<const uint4 *>(kb_ + (size_t)key * ldkv));
-                vq[t] = ldg_stream16(reinterpret_cast<const uint4 *>(vb_ + (size_t)key * ldkv));
-            }
-        }
-#pragma unroll
-        for (int t = 0; t < NT; t++) {
-            float sc = 0.0f;
-            if (ok[t]) {
-                const __half2 *hp = reinterpret_cast<const __half2 *>(&kq[t]);
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const float2 f = __half22float2(hp[e]);
-                    sc = fmaf(qv[2 * e], f.x, sc);
-                    sc = fmaf(qv[2 * e + 1], f.y, sc);
-                }
-            }
-            sc += __shfl_xor_sync(0xffffffffu, sc, 1);
-            sc += __shfl_xor_sync(0xffffffffu, sc, 2);
-            sc += __shfl_xor_sync(0xffffffffu, sc, 4);
-            if (ok[t]) {
-                const float mn = fmaxf(st.m, sc);
-                const float alpha = (st.m == -INFINITY) ? 0.0f : __expf(st.m - mn);
-                const float pw = __expf(sc - mn);
-                st.l = st.l * alpha + pw;
-                const __half2 *vp2 = reinterpret_cast<const __half2 *>(&vq[t]);
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const float2 f = __half22float2(vp2[e]);
-                    st.o[2 * e] = st.o[2 * e] * alpha + pw * f.x;
-                    st.o[2 * e + 1] = st.o[2 * e + 1] * alpha + pw * f.y;
-                }
-                st.m = mn;
-            }
+        for (int i = 0; i < 16; i++) {
+            const float4 a = __ldg(qp + i);
+            // (q . k) / sqrt(64) (attention.rs:266-267): scaling q by 1/8 first is exact (power of two)
+            const __half2 lo = __floats2half2_rn(a.x * 0.125f, a.y * 0.125f), hi = __floats2half2_rn(a.z * 0.125f, a.w * 0.125f);
+            qh[2 * i] = *reinterpret_cast<const uint32_t *>(&lo);
+            qh[2 * i + 1] = *reinterpret_cast<const uint32_t *>(&hi);
         }
     }
+    float m_run = -INFINITY, l_run = 0.0f, o[64];
 #pragma unroll
-    for (int off = 8; off <= 16; off <<= 1) {
-        const float m2 = __shfl_xor_sync(0xffffffffu, st.m, off);
-        const float l2 = __shfl_xor_sync(0xffffffffu, st.l, off);
-        float o2[8];
+    for (int j = 0; j < 64; j++) o[j] = 0.0f;
+
+    for (int it = 0; it < n_it; it++) {
+        issue(it + kDaStages - 1);
+        asm volatile("cp.async.wait_group %0;" ::"n"(kDaStages - 1) : "memory");
+        __syncwarp();                                                          // the other lanes' chunks of this stage
+        const int key = k0 + (warp + it * (kDaW)) * 32 + lane;
+        if (key < k1) {
+            const uint8_t *kr = ring_p + (size_t)(it % kDaStages) * kStage + lane * 128;
+            float sc0 = 0.0f, sc1 = 0.0f, sc2 = 0.0f, sc3 = 0.0f;
 #pragma unroll
-        for (int j = 0; j < 8; j++) o2[j] = __shfl_xor_sync(0xffffffffu, st.o[j], off);
-        soft_merge(st, m2, l2, o2);
+            for (int c = 0; c < 8; c++) {
+                const uint4 kq = *reinterpret_cast<const uint4 *>(kr + ((c ^ (lane & 7)) << 4));
+                fhfma_pair(sc0, sc1, kq.x, qh[4 * c]);
+                fhfma_pair(sc2, sc3, kq.y, qh[4 * c + 1]);
+                fhfma_pair(sc0, sc1, kq.z, qh[4 * c + 2]);
+                fhfma_pair(sc2, sc3, kq.w, qh[4 * c + 3]);
+            }
+            const float sc = (sc0 + sc1) + (sc2 + sc3);
+            if (sc > m_run) {                                                  // new running maximum: rescale (rare after the first keys)
+                const float alpha = (m_run == -INFINITY) ? 0.0f : __expf(m_run - sc);
+                l_run *= alpha;
+#pragma unroll
+                for (int j = 0; j < 64; j++) o[j] *= alpha;
+                m_run = sc;
+            }
+            // the weight as f16 (<= 1, relative rounding 2^-11) for the mixed-precision FMA; the running sum uses the same
+            // rounded value so that numerator and denominator stay consistent
+            const __half pw16 = __float2half_rn(__expf(sc - m_run));
+            l_run += __half2float(pw16);
+            const unsigned short pws = __half_as_ushort(pw16);
+            const uint8_t *vr = kr + kHalf;
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const uint4 vq = *reinterpret_cast<const uint4 *>(vr + ((c ^ (lane & 7)) << 4));
+                fhfma_scalar(o[8 * c], o[8 * c + 1], vq.x, pws);
+                fhfma_scalar(o[8 * c + 2], o[8 * c + 3], vq.y, pws);
+                fhfma_scalar(o[8 * c + 4], o[8 * c + 5], vq.z, pws);
+                fhfma_scalar(o[8 * c + 6], o[8 * c + 7], vq.w, pws);
+            }
+        }
+        __syncwarp();                                                          // stage consumed by every lane before it is refilled
     }
-    if (g == 0) {
+
+    // merge the 32 lanes of the warp: common maximum, then a butterfly reduce-scatter of the 64 outputs (62 shuffles);
+    // lane l ends up with dims 2l and 2l+1
+    float m_w = m_run;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) m_w = fmaxf(m_w, __shfl_xor_sync(0xffffffffu, m_w, off));
+    const float scl = (m_run == -INFINITY) ? 0.0f : __expf(m_run - m_w);
+    float l_w = l_run * scl;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) l_w += __shfl_xor_sync(0xffffffffu, l_w, off);
+#pragma unroll
+    for (int j = 0; j < 64; j++) o[j] *= scl;
+    float r32[32], r16[16], r8[8], r4[4], r2[2];
+    {
+        const bool up = (lane & 16) != 0;
+#pragma unroll
+        for (int j = 0; j < 32; j++) { const float mine = up ? o[32 + j] : o[j], send = up ? o[j] : o[32 + j]; r32[j] = mine + __shfl_xor_sync(0xffffffffu, send, 16); }
+    }
+    {
+        const bool up = (lane & 8) != 0;
+#pragma unroll
+        for (int j = 0; j < 16; j++) { const float mine = up ? r32[16 + j] : r32[j], send = up ? r32[j] : r32[16 + j]; r16[j] = mine + __shfl_xor_sync(0xffffffffu, send, 8); }
+    }
+    {
+        const bool up = (lane & 4) != 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) { const float mine = up ? r16[8 + j] : r16[j], send = up ? r16[j] : r16[8 + j]; r8[j] = mine + __shfl_xor_sync(0xffffffffu, send, 4); }
+    }
+    {
+        const bool up = (lane & 2) != 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) { const float mine = up ? r8[4 + j] : r8[j], send = up ? r8[j] : r8[4 + j]; r4[j] = mine + __shfl_xor_sync(0xffffffffu, send, 2); }
+    }
+    {
+        const bool up = (lane & 1) != 0;
+#pragma unroll
+        for (int j = 0; j < 2; j++) { const float mine = up ? r4[2 + j] : r4[j], send = up ? r4[j] : r4[2 + j]; r2[j] = mine + __shfl_xor_sync(0xffffffffu, send, 1); }
+    }
+    {
         float *dst = sm + warp * kPartStride;
-        if (dch == 0) { dst[64] = st.m; dst[65] = st.l; }
-#pragma unroll
-        for (int j = 0; j < 8; j++) dst[dch * 8 + j] = st.o[j];
+        if (lane == 0) { dst[64] = m_w; dst[65] = l_w; }
+        *reinterpret_cast<float2 *>(dst + 2 * lane) = make_float2(r2[0], r2[1]);
     }
     __syncthreads();
     if (warp != 0) return;
     // warp 0: merge the warps' partials (fixed order), two output dims per lane
     float M = -INFINITY;
-    for (int w2 = 0; w2 < kDaThreads / 32; w2++) M = fmaxf(M, sm[w2 * kPartStride + 64]);
+    for (int w2 = 0; w2 < kDaW; w2++) M = fmaxf(M, sm[w2 * kPartStride + 64]);
     float Lsum = 0.0f, o0 = 0.0f, o1 = 0.0f;
-    for (int w2 = 0; w2 < kDaThreads / 32; w2++) {
+    for (int w2 = 0; w2 < kDaW; w2++) {
         const float mw = sm[w2 * kPartStride + 64];
         const float sc = (mw == -INFINITY) ? 0.0f : __expf(mw - M);
         Lsum += sc * sm[w2 * kPartStride + 65];
@@ -880,7 +972,7 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P2: self-attention over the cache (attention.rs:115-119)
-        attn_phase<true>(a.q, D, sk, sv, D, (long long)a.ctx * D, kv_len, B, H, per_self, a.part, red);
+        attn_phase<true>(a.q, D, sk, sv, D, (long long)a.ctx * D, 64, kv_len, B, H, per_self, a.part, red);
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P3: out projection + residual (decoder.rs:91-92)
@@ -896,7 +988,7 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P5: cross-attention over the cached encoder K/V (attention.rs:219-233)
-        attn_phase<false>(a.q, D, ck, ck + D, 2 * D, (long long)a.T_enc * 2 * D, a.T_enc, B, H, per_cross, a.part, red);
+        attn_phase<false>(a.q, D, ck, ck + 64, 128, (long long)a.T_enc * 2 * D, (long long)a.T_enc * 128, a.T_enc, B, H, per_cross, a.part, red);
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P6: cross out projection + residual (decoder.rs:103-104)
@@ -1123,21 +1215,45 @@ int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, i
 // copy out16 for the next GEMM); one query row
 // per clip.  part: >= B*H*nsplit*68 floats, cnt: >= B*H ints (zero; left zero).  nsplit is chosen here.
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
-                                 float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
+                                 int64_t hstride, float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
                                  int64_t part_floats, int *cnt, int device, cudaStream_t st)
 {
     const int64_t units = B * H;
     if (units < 1 || kv_len < 1) return WQ4_OK;
     const int sms = wq4_sm_count(device);
-    int64_t ns = (4 * (int64_t)sms + units - 1) / units;        // ~4 CTAs per SM in flight
+    // Split only to fill the machine (two resident CTAs per SM): a split costs the partial write, a fence, an atomic and the
+    // merge by the last arriver, which a short self-attention row does not win back (measured: 15 -> 23 us at 225 keys
+    // when 640 units were split in two).
+    int64_t ns = (2 * (int64_t)sms + units - 1) / units;
     if (ns > 8) ns = 8;
-    while (ns > 1 && (kv_len + ns - 1) / ns < 32) ns--;
+    while (ns > 1 && (kv_len + ns - 1) / ns < 128) ns--;
     while (ns > 1 && units * ns * kPartStride > part_floats) ns--;
-    dim3 grid((unsigned)units, (unsigned)ns);
-    dec_attention_split_kernel<<<grid, kDaThreads, 0, st>>>(q, (int)ldq, reinterpret_cast<const __half *>(kc),
-                                                           reinterpret_cast<const __half *>(vc), (long long)ldkv,
-                                                           (long long)kv_batch_stride, out, reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len,
-                                                           (int)H, (int)ns, part, cnt);
+    const int64_t keys_per_cta = (kv_len + ns - 1) / ns;
+    const bool wide = keys_per_cta > 512;
+    static bool configured[64] = {};
+    if (!configured[device & 63]) {
+        WQ4_CUDA(cudaFuncSetAttribute(dec_attention_split_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)da_smem(8)));
+        WQ4_CUDA(cudaFuncSetAttribute(dec_attention_split_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)da_smem(2)));
+        configured[device & 63] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)units, (unsigned)ns, 1);
+    cfg.blockDim = dim3(wide ? 256 : 64, 1, 1);
+    cfg.dynamicSmemBytes = da_smem(wide ? 8 : 2);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = wq4_pdl_enabled() ? 1 : 0;
+    if (wide)
+        WQ4_CUDA(cudaLaunchKernelEx(&cfg, dec_attention_split_kernel<8>, q, (int)ldq, reinterpret_cast<const __half *>(kc),
+                                    reinterpret_cast<const __half *>(vc), (long long)ldkv, (long long)kv_batch_stride, (long long)hstride, out,
+                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, part, cnt));
+    else
+        WQ4_CUDA(cudaLaunchKernelEx(&cfg, dec_attention_split_kernel<2>, q, (int)ldq, reinterpret_cast<const __half *>(kc),
+                                    reinterpret_cast<const __half *>(vc), (long long)ldkv, (long long)kv_batch_stride, (long long)hstride, out,
+                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, part, cnt));
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

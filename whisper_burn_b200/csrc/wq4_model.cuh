@@ -7,14 +7,18 @@ struct wq4_tensor;
 
 int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y32, void *y16, int64_t rows, int64_t D,
                        cudaStream_t st);
+// K/V addressing of the decode attention kernels: element (clip b, head h, key t, dim d) sits at
+//   base + b*kv_batch_stride + h*hstride + t*ldkv + d.   Self-attention cache [B][ctx][D]: ldkv = D, hstride = 64.
+//   Cross-attention K/V, head-major [B][H][T][128] (64 K | 64 V per key, wq4m_cross_kv_pack): ldkv = 128, hstride = T*128, V = K + 64.
+int32_t wq4m_cross_kv_pack(const void *src16, void *dst16, int64_t B, int64_t T, int64_t H, cudaStream_t st);
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
-                                 float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
+                                 int64_t hstride, float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
                                  int64_t part_floats, int *cnt, int device, cudaStream_t st);
 int32_t wq4m_enc_attention(const void *qkv16, void *out16, int64_t B, int64_t T, int64_t D, int64_t H, cudaStream_t st);
 // tcgen05 implementation (wq4_attn.cu); wq4m_enc_attention dispatches to it unless WQ4_ATTN_IMPL=1 (A/B runs).
 int32_t wq4m_enc_attention_tc(const void *qkv16, void *out16, int64_t B, int64_t T, int64_t D, int64_t H, cudaStream_t st);
 int32_t wq4m_dec_attention(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
-                           float *out, int64_t ldo, int64_t B, int64_t H, int64_t q_len, int64_t kv_len, int causal_base,
+                           int64_t hstride, float *out, int64_t ldo, int64_t B, int64_t H, int64_t q_len, int64_t kv_len, int causal_base,
                            cudaStream_t st);
 int32_t wq4m_mel_transpose(const float *x, void *xt16, int64_t B, int64_t C, int64_t T, int64_t Cp, int64_t Tp, int64_t pad,
                            cudaStream_t st);
@@ -55,7 +59,7 @@ struct DecodeStepArgs {           // passed BY VALUE: the per-layer table sits i
     int kv_len;                   // self-attention cache rows valid BEFORE this step (the new row is written at kv_len)
     float *x, *q, *h, *part;      // [B][D], [B][D], [B][F], attention partials
     __half *self_k, *self_v;      // [L][B][ctx][D]
-    const __half *cross_kv;       // [L][B*T_enc][2D]
+    const __half *cross_kv;       // [L][kv_clips][H][T_enc][128] head-major, 64 K | 64 V per key (wq4m_cross_kv_pack)
     const float *lnfw, *lnfb;
     float *logits;                // [B][V]
     int arg_lo, arg_hi;           // greedy pick over [lo, hi); arg_hi <= arg_lo: no pick

@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(128) enc_attention_kernel(const __half *__rest
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) dec_attention_kernel(const float *__restrict__ q, int ldq, const __half *__restrict__ kc,
                                                             const __half *__restrict__ vc, int ldkv, long long kv_batch_stride,
-                                                            float *__restrict__ out, int ldo, int q_len, int kv_len,
+                                                            long long hstride, float *__restrict__ out, int ldo, int q_len, int kv_len,
                                                             int causal_base /* <0: not causal */)
 {
     extern __shared__ float sm_scores[];   // [kv_len] + 64 q + 256*... partials
@@ -343,8 +343,8 @@ __global__ void __launch_bounds__(256) dec_attention_kernel(const float *__restr
     const float *qrow = q + ((size_t)b * q_len + qi) * ldq + h * kHD;
     if (tid < kHD) sq[tid] = qrow[tid];
     __syncthreads();
-    const __half *kb = kc + (size_t)b * kv_batch_stride + h * kHD;
-    const __half *vb = vc + (size_t)b * kv_batch_stride + h * kHD;
+    const __half *kb = kc + (size_t)b * kv_batch_stride + (size_t)h * hstride;      // hstride: 64 inside a [ctx][D] row, T*128 head-major
+    const __half *vb = vc + (size_t)b * kv_batch_stride + (size_t)h * hstride;
     // scores: one thread per key (128-byte contiguous row read)
     float lmax = -INFINITY;
     for (int key = tid; key < visible; key += 256) {
@@ -527,9 +527,37 @@ __global__ void kv_append_kernel(const float *__restrict__ kv, int ld_src, __hal
     }
 }
 
+// Cross-attention K/V of one decoder layer, [B*T][2D] f16 as the fused key|value projection writes it (attention.rs:185-186)
+// -> head-major [B][H][T][128] (64 K | 64 V per key): a (clip, head) unit of the decode-step attention then reads ONE
+// contiguous 384 KB stream instead of 128-byte chunks 5 KB apart (HBM ran at ~4.5 TB/s on the strided form).  One thread moves
+// one 16-byte chunk; reads are fully coalesced rows, writes are whole 128-byte lines.
+__global__ void __launch_bounds__(256) cross_kv_pack_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, int T, int H,
+                                                            long long total_chunks)
+{
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;      // chunk index in the source: [b*T + t][2][H][8]
+    if (i >= total_chunks) return;
+    const int c = (int)(i & 7);
+    long long r = i >> 3;
+    const int h = (int)(r % H); r /= H;
+    const int kv = (int)(r & 1); r >>= 1;                               // 0 = key half of the row, 1 = value half
+    const int t = (int)(r % T);
+    const long long b = r / T;
+    dst[(((b * H + h) * T + t) * 2 + kv) * 8 + c] = src[i];
+}
+
 }  // namespace
 
 // ---- host launchers ------------------------------------------------------------------------------
+int32_t wq4m_cross_kv_pack(const void *src16, void *dst16, int64_t B, int64_t T, int64_t H, cudaStream_t st)
+{
+    const long long chunks = (long long)B * T * 2 * H * 8;
+    cross_kv_pack_kernel<<<(unsigned)((chunks + 255) / 256), 256, 0, st>>>(reinterpret_cast<const uint4 *>(src16),
+                                                                          reinterpret_cast<uint4 *>(dst16), (int)T, (int)H, chunks);
+    wq4_count_launch();
+    WQ4_CUDA(cudaGetLastError());
+    return WQ4_OK;
+}
+
 int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y32, void *y16, int64_t rows, int64_t D,
                        cudaStream_t st)
 {
@@ -578,15 +606,15 @@ int32_t wq4m_enc_attention(const void *qkv16, void *out16, int64_t B, int64_t T,
 }
 
 int32_t wq4m_dec_attention(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
-                           float *out, int64_t ldo, int64_t B, int64_t H, int64_t q_len, int64_t kv_len, int causal_base,
-                           cudaStream_t st)
+                           int64_t hstride, float *out, int64_t ldo, int64_t B, int64_t H, int64_t q_len, int64_t kv_len,
+                           int causal_base, cudaStream_t st)
 {
     dim3 grid((unsigned)q_len, (unsigned)H, (unsigned)B);
     size_t smem = (size_t)(((kv_len + 3) & ~3) + kHD + 4 * 64 + 8) * sizeof(float);
     WqProfScope prof(WQ4_PROF_ATTN_DEC, (double)B * (double)H * (double)kv_len * 64.0 * 2.0 * 2.0, st);
     dec_attention_kernel<<<grid, 256, smem, st>>>(q, (int)ldq, reinterpret_cast<const __half *>(kc),
-                                                  reinterpret_cast<const __half *>(vc), (int)ldkv, (long long)kv_batch_stride, out,
-                                                  (int)ldo, (int)q_len, (int)kv_len, causal_base);
+                                                  reinterpret_cast<const __half *>(vc), (int)ldkv, (long long)kv_batch_stride,
+                                                  (long long)hstride, out, (int)ldo, (int)q_len, (int)kv_len, causal_base);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

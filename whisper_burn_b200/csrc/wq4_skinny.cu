@@ -1,10 +1,15 @@
-// wq4_skinny.cu -- Q4_0 linear for a handful of activation rows (9..64): decode steps of batches beyond the single-kernel
-// step and decoder prompt passes (Q4Linear::forward at M = batch, src/gguf/linear.rs:34-40; shader.wgsl:51-92).
+// wq4_skinny.cu -- Q4_0 linear for a handful of activation rows (default 9..16, up to 64 on request): decode steps of batches
+// just beyond the single-kernel step and short decoder prompt passes (Q4Linear::forward at M = batch,
+// src/gguf/linear.rs:34-40; shader.wgsl:51-92).
 //
-// The CTA-pair tcgen05 GEMM tiles N in units of 256 weight rows, so at N = 1280 it runs on 10 of the 148 SMs and a
-// 32-row decode GEMM takes 12-15 us although its 0.9 MB of Q4 bytes stream in 0.15 us.  Here the weight rows are dealt out
-// 16 per CTA (80..320 CTAs), the eight warps of a CTA split K, and the product runs on mma.sync m16n8k16 with the WEIGHT rows
-// as the MMA M dimension and the activation rows as N (8 per n-tile):
+// The CTA-pair tcgen05 GEMM tiles N in units of 256 weight rows and walks K serially, so at N = 1280 it runs on 10 of the
+// 148 SMs whatever the row count (5.5 us at K = 1280, 16.4 us at K = 5120, back to back).  Here the weight rows are dealt out
+// 16 per CTA (80..320 CTAs), the warps of a CTA split K, and the product runs on mma.sync m16n8k16 with the WEIGHT rows
+// as the MMA M dimension and the activation rows as N (8 per n-tile).  Measured at 16 rows: 3.4 / 4.8 / 5.0 us for
+// N = 1280 / 3840 / 5120 at K = 1280 (profiles/r01_microbench_skinny.txt).  Every CTA re-reads all activation rows, so the
+// advantage is gone by 32 rows (x traffic = N/16 * rows * K * 2 bytes out of L2) and the default dispatch stops at 16.  A
+// variant with 128-row CTAs, bulk-copy staging and the K split over a thread-block cluster was measured slower at every
+// size (cluster launch and the DSMEM exchange cost more than they saved) and dropped.
 //   * A fragment straight from the panel layout, no shared memory: lane (g = lane/4, t = lane%4) loads word t of the
 //     32-nibble block of rows g and g+8 -- a warp reads 2 x 128 contiguous bytes per block -- and the four half2 pairs of
 //     the word (lop3 + 0x6400 trick, exact nib-8, times the f16 block scale) are the a0..a3 registers of two k16 steps.
@@ -23,9 +28,8 @@
 
 namespace {
 
-constexpr int kST = 256;            // threads per CTA
-constexpr int kSW = kST / 32;       // warps = K split
 constexpr int kSRows = 16;          // weight rows per CTA
+__host__ __device__ constexpr int sk_max_warps(int nt) { return nt <= 4 ? 16 : 8; }   // K split; 16 warps when K >= 2048
 
 struct SkinnyParams {
     const uint4 *nib;
@@ -88,16 +92,19 @@ __device__ __forceinline__ void word_pairs(uint32_t w, __half2 d2, uint32_t (&o)
 }
 
 template <int NT, int XMODE>
-__global__ void __launch_bounds__(kST) q4_skinny_kernel(const SkinnyParams p)
+__global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const SkinnyParams p)
 {
     constexpr int RP = 8 * NT + 1;                       // padded row pitch of the reduction buffer (floats)
-    __shared__ float red[kSW * kSRows * RP];
+    __shared__ float red[sk_max_warps(NT) * kSRows * RP];
+    const int kST = blockDim.x, kSW = kST >> 5;
     __shared__ float s_mean[XMODE == 2 ? 8 * NT : 1], s_rstd[XMODE == 2 ? 8 * NT : 1];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
     const int row0 = blockIdx.x * kSRows;                // first weight row of this CTA
     const int panel = row0 >> 7, rin = row0 & 127;
     const int K = p.k;
+    ptx::grid_dep_launch();     // PDL: the next kernel of the decode chain may be scheduled
+    ptx::grid_dep_wait();       // x / residual come from the previous kernel
 
     if (XMODE == 2) {
         // LayerNorm statistics of every activation row (same summation order as layernorm_kernel)
@@ -136,7 +143,7 @@ __global__ void __launch_bounds__(kST) q4_skinny_kernel(const SkinnyParams p)
     }
 
     const size_t slab = (size_t)panel * p.kbp;
-#pragma unroll 2
+#pragma unroll(NT == 2 ? 4 : (NT == 4 ? 2 : 1))
     for (int kbi = warp; kbi < p.kb; kbi += kSW) {
         const uint32_t *wp = reinterpret_cast<const uint32_t *>(p.nib + (slab + kbi) * WQ4_PANEL_ROWS + rin);
         const uint32_t w_lo = ldg_nc32(wp + lane);            // rows g     (lane = 4g + t: word t of row g)
@@ -205,7 +212,6 @@ __global__ void __launch_bounds__(kST) q4_skinny_kernel(const SkinnyParams p)
         const int r = o & (kSRows - 1), m = o >> 4, nn = row0 + r;
         if (nn >= p.n) continue;
         float s = 0.0f;
-#pragma unroll
         for (int w2 = 0; w2 < kSW; w2++) s += red[w2 * (kSRows * RP) + r * RP + m];      // fixed order
         if (p.bias) s += __ldg(p.bias + nn);
         if (p.flags & WQ4_EPI_GELU) s = wq4_gelu_tanh(s);
@@ -224,15 +230,26 @@ __global__ void __launch_bounds__(kST) q4_skinny_kernel(const SkinnyParams p)
 template <int NT>
 int32_t launch_nt(const SkinnyParams &p, int mode, unsigned grid, cudaStream_t st)
 {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3((p.kb >= 64 ? sk_max_warps(NT) : 8) * 32, 1, 1);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = wq4_pdl_enabled() ? 1 : 0;
     switch (mode) {
-    case 0: q4_skinny_kernel<NT, 0><<<grid, kST, 0, st>>>(p); break;
-    case 1: q4_skinny_kernel<NT, 1><<<grid, kST, 0, st>>>(p); break;
-    default: q4_skinny_kernel<NT, 2><<<grid, kST, 0, st>>>(p); break;
+    case 0: WQ4_CUDA(cudaLaunchKernelEx(&cfg, q4_skinny_kernel<NT, 0>, p)); break;
+    case 1: WQ4_CUDA(cudaLaunchKernelEx(&cfg, q4_skinny_kernel<NT, 1>, p)); break;
+    default: WQ4_CUDA(cudaLaunchKernelEx(&cfg, q4_skinny_kernel<NT, 2>, p)); break;
     }
     return WQ4_OK;
 }
 
 }  // namespace
+
+bool wq4_skinny_supported(const wq4_tensor *w, int64_t rows) { return w && w->matrix_mode && rows >= 1 && rows <= WQ4_SKINNY_MAX_ROWS; }
 
 int32_t wq4_launch_skinny(const LinearArgs &a, const SkinnyExtra *ex)
 {
@@ -254,9 +271,11 @@ int32_t wq4_launch_skinny(const LinearArgs &a, const SkinnyExtra *ex)
     const int mode = a.x_f16 ? 0 : (ln ? 2 : 1);
     const unsigned grid = (unsigned)((w->n + kSRows - 1) / kSRows);
     WqProfScope prof(WQ4_PROF_GEMM_Q4, 2.0 * (double)a.rows * (double)w->n * (double)w->k, a.stream);
-    if (a.rows <= 16) launch_nt<2>(p, mode, grid, a.stream);
-    else if (a.rows <= 32) launch_nt<4>(p, mode, grid, a.stream);
-    else launch_nt<8>(p, mode, grid, a.stream);
+    int32_t st;
+    if (a.rows <= 16) st = launch_nt<2>(p, mode, grid, a.stream);
+    else if (a.rows <= 32) st = launch_nt<4>(p, mode, grid, a.stream);
+    else st = launch_nt<8>(p, mode, grid, a.stream);
+    if (st != WQ4_OK) return st;
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

@@ -154,7 +154,7 @@ struct wq4_whisper {
     float *x = nullptr, *enc32 = nullptr;
     int64_t Cp1 = 0, Tp1 = 0, Tp2 = 0;
     // decoder state
-    __half *cross_kv = nullptr;      // [L][B*T_enc][2D]
+    __half *cross_kv = nullptr;      // [L][B][H][T_enc][128]: head-major, 64 K | 64 V per key
     __half *self_k = nullptr, *self_v = nullptr;   // [L][B][n_text_ctx][D]
     float *dx = nullptr, *dxn = nullptr, *dqkv = nullptr, *datt = nullptr, *dq = nullptr, *dh = nullptr, *logits = nullptr;
     __half *dxn16 = nullptr, *datt16 = nullptr, *dh16 = nullptr;   // f16 operands of the decoder GEMMs (rows > 8)
@@ -492,7 +492,11 @@ int32_t cross_kv(wq4_whisper *m, int64_t B, cudaStream_t st)
 {
     const int64_t D = m->D, M = B * m->T_enc;
     for (size_t l = 0; l < m->dec.size(); l++)
-        CHK(lin16(m->dec[l].ckv, m->enc16, nullptr, m->cross_kv + l * (size_t)M * 2 * D, nullptr, M, 0, st));
+    {
+        // projection into the (now idle) encoder q|k|v buffer, then repacked head-major [B][H][T][128] for the decode steps
+        CHK(lin16(m->dec[l].ckv, m->enc16, nullptr, m->qkv16, nullptr, M, 0, st));
+        CHK(wq4m_cross_kv_pack(m->qkv16, m->cross_kv + l * (size_t)M * 2 * D, B, m->T_enc, m->cfg.n_text_head, st));
+    }
     return WQ4_OK;
 }
 
@@ -571,18 +575,18 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         auto lin_att = [&](const Lin &l) {                                             // input: attention output, + residual
             return f16p ? lin16(l, m->datt16, m->dx, nullptr, m->dx, R, 0, st) : lin32(m, l, m->datt, m->dx, m->dx, R, 0, st);
         };
-        if (f16p && R <= WQ4_SKINNY_MAX_ROWS && use_skinny_step()) {
-            // Single-query step of 9..64 clips: eight launches per layer.  The skinny linear applies LayerNorm on load
+        if (f16p && R <= WQ4_SKINNY_DEFAULT_ROWS && use_skinny_step()) {
+            // Single-query step of 9..16 clips: eight launches per layer (beyond 16 rows the tcgen05 GEMM is faster).  The skinny linear applies LayerNorm on load
             // (q|k|v, cross-q, fc1), appends the new K/V rows to the f16 cache from the q|k|v epilogue and adds the
             // residual in place; the split-KV attention emits the f16 operand of the following projection.
             SkinnyExtra none = {}, kv = {};
             kv.kc = sk; kv.vc = sv; kv.kv_batch_stride = ctx * D; kv.kv_ld = D; kv.kv_pos = kv_pos0; kv.kv_d = D;
             CHK(lin_sk(L.qkv, m->dx, nullptr, &L.attn_ln, m->dqkv, nullptr, nullptr, R, 0, kv, st));
-            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, m->datt16, D, B, H, kv_pos0 + 1,
+            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, m->datt16, D, B, H, kv_pos0 + 1,
                                          m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
             CHK(lin_sk(L.out, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
             CHK(lin_sk(L.cq, m->dx, nullptr, &L.cross_ln, m->dq, nullptr, nullptr, R, 0, none, st));
-            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, m->datt16, D, B, H,
+            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, m->datt16, D, B, H,
                                          m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
             CHK(lin_sk(L.cout, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
             CHK(lin_sk(L.fc1, m->dx, nullptr, &L.mlp_ln, nullptr, m->dh16, nullptr, R, WQ4_EPI_GELU, none, st));
@@ -594,20 +598,20 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         CHK(lin_n(L.qkv, m->dqkv, nullptr, 0));
         CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
         if (q_len == 1 && m->da_part)
-            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, f16p ? m->datt16 : nullptr, D, B, H, kv_pos0 + 1,
+            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, f16p ? m->datt16 : nullptr, D, B, H, kv_pos0 + 1,
                                          m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
         else
-            CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, m->datt, D, B, H, q_len, kv_pos0 + q_len,
+            CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, D, B, H, q_len, kv_pos0 + q_len,
                                    q_len > 1 ? (int)kv_pos0 : -1, st));
         CHK(lin_att(L.out));
         // cross-attention over the cached encoder K/V (decoder.rs:95-104)
         CHK(ln(L.cross_ln));
         CHK(lin_n(L.cq, m->dq, nullptr, 0));
         if (q_len == 1 && m->da_part)
-            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, f16p ? m->datt16 : nullptr, D, B, H,
+            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, f16p ? m->datt16 : nullptr, D, B, H,
                                          m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
         else
-            CHK(wq4m_dec_attention(m->dq, D, ck, ck + D, 2 * D, m->T_enc * 2 * D, m->datt, D, B, H, q_len, m->T_enc, -1, st));
+            CHK(wq4m_dec_attention(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, D, B, H, q_len, m->T_enc, -1, st));
         CHK(lin_att(L.cout));
         // FFN (decoder.rs:107-110)
         CHK(ln(L.mlp_ln));
