@@ -134,10 +134,11 @@ def tiny8():
 
 @pytest.mark.parametrize("batch", [1, 2, 4, 5, 8, 11, 19, 26])
 def test_decode_step_kernel_every_batch_size(tiny8, batch):
-    """The one-kernel decode step (csrc/wq4_decode.cu, templates R = 1, 2, 4, 8; batch 5 runs the R = 8 code with three
-    idle rows; batches 11 and 19 run it once per group of 8 clips on offset cache pointers; batch 26 takes the per-op path with the
-    split-KV attention kernel) against the oracle clip by clip: different audio and different tokens per clip, so a wrong batch index,
-    cache row or split-KV segment shows up as a logit mismatch."""
+    """Decode steps at every batch size against the oracle clip by clip: different audio and different tokens per clip, so a
+    wrong batch index, cache offset or split-KV merge shows.  Batches 1, 2, 4 run the one-kernel decode step (csrc/wq4_decode.cu,
+    templates R = 1, 2, 4); 5, 8 and 11 the per-op path on the skinny linear (fused LayerNorm, cache append in the q|k|v
+    epilogue, csrc/wq4_skinny.cu); 19 and 26 the per-op path on the tcgen05 GEMM; all per-op batches use the key-per-lane
+    attention kernel.  The R = 8 template and the grouped launch of the one-kernel step are covered by the child-process test below."""
     cfg, oracle, model = tiny8
     mel = wn.synthetic_mel(batch, cfg.n_mels, 3000, seed=40 + batch)
     model.encode(torch.from_numpy(mel).to(DEV), want_output=False)

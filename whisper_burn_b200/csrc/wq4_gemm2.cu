@@ -535,6 +535,9 @@ int wq4_pick_tile_m2(int64_t rows, int64_t npairs)
         forced = e ? atoi(e) : 0;
     }
     if (forced == 64 || forced == 128 || forced == 192 || forced == 256) return forced;
+    // One row tile or less: such launches are a single serial walk over K per CTA pair, and a K stage costs
+    // 8 x (36 + TILE_M/2) clk of MMA issue, so the narrowest tile is the fastest (decode steps of 17..64 clips)
+    if (rows <= 64) return 64;
     const int pairs = 74;
     int best = 64;
     double best_cost = 1e30;

@@ -403,7 +403,7 @@ int32_t reserve(wq4_whisper *m, int64_t B)
         m->Vp = (m->V + 31) / 32 * 32;
         CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
         CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
-        if (B > 8) {   // batches that can exceed one decode group take the per-op path
+        if (B > 4) {   // batches beyond the single-kernel step take the per-op path
             m->Vp256 = (m->V + 255) / 256 * 256;
             CHK(dev_alloc(m, &m->tok_emb16, (size_t)m->Vp256 * D));
             WQ4_CUDA(cudaMemset(m->tok_emb16, 0, (size_t)m->Vp256 * D * 2));
@@ -516,13 +516,23 @@ static bool use_decode_kernel()
 // kernel once per group, back to back on the stream: the caches are laid out [layer][B][..] so a group is a pointer
 // offset, and the kernel takes the layer stride (kv_clips) separately from its own batch.
 constexpr int64_t kDecodeGroup = 8;
-// Largest batch that runs as groups of 8 through the single-kernel step.  Measured (profiles/r01_decode_step.txt): beyond
-// one group the per-op path, which reads the weights once per step and uses the split-KV attention kernel, is faster
-// (batch 16: 4.8 ms against 2 x 3.1 ms), so the default is a single group; WQ4_DECODE_GROUP_MAX overrides it (tests).
+// Largest batch that runs through the single-kernel step (in groups of 8 when an override allows more).  Measured
+// (profiles/r01_decode_step.txt): the persistent kernel wins up to 4 clips (1.49 / 1.83 / 2.29 ms at 1 / 2 / 4); from 5 clips
+// on the per-op path -- skinny linear with fused LayerNorm and cache append, key-per-lane attention kernel, 8 launches per
+// layer -- is faster (2.31 ms at 5, 2.61 ms against 3.04 ms at 8), so the default is 4; WQ4_DECODE_GROUP_MAX overrides it (tests).
+// Smallest row count of the per-op path that runs on f16 operands (skinny linear / tcgen05 GEMM); below it the f32 GEMV.
+// WQ4_DECODE_F16_MIN overrides it (tuning runs together with WQ4_DECODE_GROUP_MAX).
+static int64_t decode_f16_min_rows()
+{
+    static int64_t v = -1;
+    if (v < 0) { const char *e = getenv("WQ4_DECODE_F16_MIN"); v = e ? atoll(e) : 5; if (v < 1) v = 1; }
+    return v;
+}
+
 static int64_t decode_grouped_max()
 {
     static int64_t v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); v = e ? atoll(e) : kDecodeGroup; if (v < 1) v = 1; }
+    if (v < 0) { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); v = e ? atoll(e) : 4; if (v < 1) v = 1; }
     return v;
 }
 
@@ -567,7 +577,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         const __half *ck = m->cross_kv + l * (size_t)M * 2 * D;
         // Rows > 8 run on the tensor-core GEMM, whose operand is f16: the producers (LayerNorm, split attention, fc1's
         // epilogue) emit it directly; rows <= 8 use the f32 GEMV.  (f16p = single-query step on the GEMM path.)
-        const bool g16 = R > 8, f16p = g16 && q_len == 1 && m->da_part;
+        const bool g16 = R >= decode_f16_min_rows(), f16p = g16 && q_len == 1 && m->da_part;
         auto ln = [&](const LNp &w) { return wq4m_layernorm(m->dx, w.w, w.b, g16 ? nullptr : m->dxn, g16 ? m->dxn16 : nullptr, R, D, st); };
         auto lin_n = [&](const Lin &l, float *y32, void *y16, uint32_t flags) {       // input: the LayerNorm output
             return g16 ? lin16(l, m->dxn16, y32, y16, nullptr, R, flags, st) : lin32(m, l, m->dxn, y32, nullptr, R, flags, st);
@@ -624,7 +634,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         }
     }
     // final LN on the last position of every clip, then logits = x . token_embedding^T (decoder.rs:286-292)
-    if (R > 8 && m->tok_emb16) {
+    if (R >= decode_f16_min_rows() && m->tok_emb16) {
         // batches above one decode group: the logits are one tensor-core GEMM on the f16 embedding rows
         const void *last16 = m->dxn16;
         if (q_len == 1) {
@@ -640,7 +650,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         ga.x_k = D; ga.x_rows = B; ga.x_batch = 1; ga.x_row_stride = D; ga.x_batch_stride = B * D;
         ga.ob = B * m->V; ga.ot = m->V; ga.on = 1;
         ga.device = m->device; ga.stream = st;
-        CHK(wq4_launch_gemm_dense(ga, B <= 32 ? 32 : 64));
+        CHK(wq4_launch_gemm_dense(ga, B <= 32 ? 32 : 64));   // row tile of the first-generation kernel
     } else {
         if (q_len == 1) {
             CHK(wq4m_layernorm(m->dx, m->ln.w, m->ln.b, m->dxn, nullptr, B, D, st));
