@@ -108,8 +108,34 @@ __global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const 
 
     if (XMODE == 2) {
         // LayerNorm statistics of every activation row (same summation order as layernorm_kernel)
+        const bool in_regs = (K & 127) == 0 && K <= 2048;     // the row fits 16 float4 per lane: one pass over global memory
         for (int m = warp; m < p.rows; m += kSW) {
             const float4 *xr = reinterpret_cast<const float4 *>(p.x32 + (size_t)m * K);
+            if (in_regs) {
+                float4 v[16];
+                const int ni = K >> 7;
+                float s = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    if (i < ni) v[i] = xr[i * 32 + lane];
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    if (i < ni) s += v[i].x + v[i].y + v[i].z + v[i].w;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                const float mean = s / (float)K;
+                float q = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    if (i < ni) {
+                        const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+                        q += a * a + b * b + c * c + d * d;
+                    }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+                if (lane == 0) { s_mean[m] = mean; s_rstd[m] = 1.0f / sqrtf(q / (float)K + 1e-5f); }
+                continue;
+            }
             float s = 0.0f;
             for (int i = lane; i < K / 4; i += 32) { const float4 v = xr[i]; s += v.x + v.y + v.z + v.w; }
 #pragma unroll

@@ -627,7 +627,12 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         CHK(ln(L.mlp_ln));
         if (g16) {
             CHK(lin16(L.fc1, m->dxn16, nullptr, m->dh16, nullptr, R, WQ4_EPI_GELU, st));
-            CHK(lin16(L.fc2, m->dh16, m->dx, nullptr, m->dx, R, 0, st));
+            // fc2 (K = 4D) at 17..32 rows: the skinny kernel's 16-warp K split (11.6 us) beats the serial K walk of the
+            // tcgen05 kernel on 10 SMs (16.4 us, profiles/r01_microbench_skinny.txt)
+            if (R <= 32 && L.fc2.w->k >= 4096 && use_skinny_step())
+                CHK(lin_sk(L.fc2, nullptr, m->dh16, nullptr, m->dx, nullptr, m->dx, R, 0, SkinnyExtra{}, st));
+            else
+                CHK(lin16(L.fc2, m->dh16, m->dx, nullptr, m->dx, R, 0, st));
         } else {
             CHK(lin32(m, L.fc1, m->dxn, m->dh, nullptr, R, WQ4_EPI_GELU, st));
             CHK(lin32(m, L.fc2, m->dh, m->dx, m->dx, R, 0, st));
