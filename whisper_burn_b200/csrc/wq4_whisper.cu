@@ -442,6 +442,13 @@ int32_t lin_sk(const Lin &l, const float *x32, const void *x16, const LNp *ln, f
     if (ln) { ex.ln_w = ln->w; ex.ln_b = ln->b; }
     return wq4_launch_skinny(a, &ex);
 }
+// Largest batch whose decode step runs entirely on the skinny linear; WQ4_SKINNY_STEP_ROWS overrides it (tuning runs).
+static int64_t skinny_step_rows()
+{
+    static int64_t v = -1;
+    if (v < 0) { const char *e = getenv("WQ4_SKINNY_STEP_ROWS"); v = e ? atoll(e) : WQ4_SKINNY_DEFAULT_ROWS; if (v > WQ4_SKINNY_MAX_ROWS) v = WQ4_SKINNY_MAX_ROWS; }
+    return v;
+}
 static bool use_skinny_step()
 {
     static int v = -1;
@@ -585,7 +592,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         auto lin_att = [&](const Lin &l) {                                             // input: attention output, + residual
             return f16p ? lin16(l, m->datt16, m->dx, nullptr, m->dx, R, 0, st) : lin32(m, l, m->datt, m->dx, m->dx, R, 0, st);
         };
-        if (f16p && R <= WQ4_SKINNY_DEFAULT_ROWS && use_skinny_step()) {
+        if (f16p && R <= skinny_step_rows() && use_skinny_step()) {
             // Single-query step of 9..16 clips: eight launches per layer (beyond 16 rows the tcgen05 GEMM is faster).  The skinny linear applies LayerNorm on load
             // (q|k|v, cross-q, fc1), appends the new K/V rows to the f16 cache from the q|k|v epilogue and adds the
             // residual in place; the split-KV attention emits the f16 operand of the following projection.
