@@ -622,7 +622,7 @@ template <int kDaW>
 __global__ void __launch_bounds__(kDaW * 32, kDaW == 8 ? 1 : 4)
 dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *__restrict__ kc, const __half *__restrict__ vc,
                            long long ldkv, long long bstride, long long hstride, float *__restrict__ out, __half *__restrict__ out16, int ldo, int kv_len,
-                           int H, int nsplit,
+                           int H, int nsplit, int append_off,
                            float *__restrict__ part, int *__restrict__ cnt)
 {
     __shared__ float sm[(kDaW) * kPartStride];
@@ -633,6 +633,26 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
     const int k0 = sp * per, k1 = min(kv_len, k0 + per);
     ptx::grid_dep_launch();     // PDL: the following projection may be scheduled and prefetch its weights
     ptx::grid_dep_wait();       // q and the new K/V row come from the previous kernel
+
+    // Optional cache append (self-attention of a decode step, attention.rs:106-113 without the realloc): q points into the
+    // fused q|k|v projection output and the new key / value of this (clip, head) sit append_off / 2*append_off floats
+    // further.  The split that owns the newest key stores them (f16, saturating, as kv_append_kernel does) before it
+    // starts streaming, which removes the separate append launch.
+    if (append_off > 0 && k0 < k1 && k1 == kv_len) {
+        if (threadIdx.x < 16) {
+            const int isv = threadIdx.x >> 3, c = threadIdx.x & 7;
+            const float *src = q + (size_t)b * ldq + (size_t)(1 + isv) * append_off + h * 64 + c * 8;
+            const float4 a = __ldcg(reinterpret_cast<const float4 *>(src)), d = __ldcg(reinterpret_cast<const float4 *>(src) + 1);
+            uint4 pk;
+            pk.x = (uint32_t)f32_to_f16_sat_d(a.x) | ((uint32_t)f32_to_f16_sat_d(a.y) << 16);
+            pk.y = (uint32_t)f32_to_f16_sat_d(a.z) | ((uint32_t)f32_to_f16_sat_d(a.w) << 16);
+            pk.z = (uint32_t)f32_to_f16_sat_d(d.x) | ((uint32_t)f32_to_f16_sat_d(d.y) << 16);
+            pk.w = (uint32_t)f32_to_f16_sat_d(d.z) | ((uint32_t)f32_to_f16_sat_d(d.w) << 16);
+            __half *dst = const_cast<__half *>(isv ? vc : kc) + (size_t)b * bstride + (size_t)h * hstride + (size_t)(kv_len - 1) * ldkv + c * 8;
+            *reinterpret_cast<uint4 *>(dst) = pk;
+        }
+        __syncthreads();
+    }
 
     // ONE KEY PER LANE.  The first form of this kernel spread a key over 8 lanes (8 dims each): three shuffles, two
     // exponentials and the loop overhead per key quad made it issue bound -- 24 M warp instructions, 52 % issue-active with
@@ -1216,7 +1236,7 @@ int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, i
 // per clip.  part: >= B*H*nsplit*68 floats, cnt: >= B*H ints (zero; left zero).  nsplit is chosen here.
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
                                  int64_t hstride, float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
-                                 int64_t part_floats, int *cnt, int device, cudaStream_t st)
+                                 int64_t part_floats, int *cnt, int device, cudaStream_t st, int64_t append_off)
 {
     const int64_t units = B * H;
     if (units < 1 || kv_len < 1) return WQ4_OK;
@@ -1249,11 +1269,11 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
     if (wide)
         WQ4_CUDA(cudaLaunchKernelEx(&cfg, dec_attention_split_kernel<8>, q, (int)ldq, reinterpret_cast<const __half *>(kc),
                                     reinterpret_cast<const __half *>(vc), (long long)ldkv, (long long)kv_batch_stride, (long long)hstride, out,
-                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, part, cnt));
+                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, (int)append_off, part, cnt));
     else
         WQ4_CUDA(cudaLaunchKernelEx(&cfg, dec_attention_split_kernel<2>, q, (int)ldq, reinterpret_cast<const __half *>(kc),
                                     reinterpret_cast<const __half *>(vc), (long long)ldkv, (long long)kv_batch_stride, (long long)hstride, out,
-                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, part, cnt));
+                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, (int)append_off, part, cnt));
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

@@ -613,13 +613,14 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         // self-attention with cache (decoder.rs:84-92 / 147-152)
         CHK(ln(L.attn_ln));
         CHK(lin_n(L.qkv, m->dqkv, nullptr, 0));
-        CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
-        if (q_len == 1 && m->da_part)
+        if (q_len == 1 && m->da_part)           // the attention kernel appends the new K/V row itself
             CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, f16p ? m->datt16 : nullptr, D, B, H, kv_pos0 + 1,
-                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
-        else
+                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st, D));
+        else {
+            CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
             CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, D, B, H, q_len, kv_pos0 + q_len,
                                    q_len > 1 ? (int)kv_pos0 : -1, st));
+        }
         CHK(lin_att(L.out));
         // cross-attention over the cached encoder K/V (decoder.rs:95-104)
         CHK(ln(L.cross_ln));
