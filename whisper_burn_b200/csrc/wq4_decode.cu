@@ -632,7 +632,10 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
     const int per = (kv_len + nsplit - 1) / nsplit;
     const int k0 = sp * per, k1 = min(kv_len, k0 + per);
     ptx::grid_dep_launch();     // PDL: the following projection may be scheduled and prefetch its weights
-    ptx::grid_dep_wait();       // q and the new K/V row come from the previous kernel
+    // append_off < 0: the K/V rows are static (cross-attention over the encoder K/V), so the first ring stages are requested
+    // BEFORE waiting for the previous kernel and only q is read after the wait
+    const bool static_kv = append_off < 0;
+    if (!static_kv) ptx::grid_dep_wait();       // q and the new K/V row come from the previous kernel
 
     // Optional cache append (self-attention of a decode step, attention.rs:106-113 without the realloc): q points into the
     // fused q|k|v projection output and the new key / value of this (clip, head) sit append_off / 2*append_off floats
@@ -694,6 +697,7 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
     };
 #pragma unroll
     for (int s2 = 0; s2 < kDaStages - 1; s2++) issue(s2);
+    if (static_kv) ptx::grid_dep_wait();        // q comes from the previous kernel
 
     // q as packed f16 pairs: the products run on the mixed-precision FMA of sm_100 (fma.rn.f32.f16 -> FHFMA: f16 x f16 + f32,
     // operand halves addressed in place), which removes the 128 half->float conversions per key that made up a fifth of

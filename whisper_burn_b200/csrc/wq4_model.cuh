@@ -14,6 +14,7 @@ int32_t wq4m_cross_kv_pack(const void *src16, void *dst16, int64_t B, int64_t T,
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
                                  int64_t hstride, float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
                                  int64_t part_floats, int *cnt, int device, cudaStream_t st, int64_t append_off = 0);
+// append_off < 0: K/V are static (cross-attention): their first ring stages are requested before the programmatic-launch wait.
 // append_off > 0: q points into a fused q|k|v row and the kernel first stores the new key / value (q + append_off,
 // q + 2*append_off) of every (clip, head) at cache row kv_len - 1 -- the cache append of a decode step without its own launch.
 int32_t wq4m_enc_attention(const void *qkv16, void *out16, int64_t B, int64_t T, int64_t D, int64_t H, cudaStream_t st);

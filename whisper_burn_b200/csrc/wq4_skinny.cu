@@ -104,6 +104,16 @@ __global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const 
     const int panel = row0 >> 7, rin = row0 & 127;
     const int K = p.k;
     ptx::grid_dep_launch();     // PDL: the next kernel of the decode chain may be scheduled
+    // The weights do not depend on the previous kernel: pull this warp's blocks (two 128-byte nibble lines and the scale line
+    // per block) into L2 while the predecessor is still running, so that the loads after the wait do not pay the HBM latency.
+    if (lane < 3) {
+        const size_t slab0 = (size_t)panel * p.kbp;
+        for (int kbi = warp; kbi < p.kb; kbi += kSW) {
+            const char *base = lane < 2 ? reinterpret_cast<const char *>(p.nib + (slab0 + kbi) * WQ4_PANEL_ROWS + rin) + lane * 128
+                                        : reinterpret_cast<const char *>(p.scl + (slab0 + kbi) * WQ4_PANEL_ROWS + rin);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base));
+        }
+    }
     ptx::grid_dep_wait();       // x / residual come from the previous kernel
 
     if (XMODE == 2) {

@@ -605,7 +605,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
             CHK(lin_sk(L.out, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
             CHK(lin_sk(L.cq, m->dx, nullptr, &L.cross_ln, m->dq, nullptr, nullptr, R, 0, none, st));
             CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, m->datt16, D, B, H,
-                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1));
             CHK(lin_sk(L.cout, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
             CHK(lin_sk(L.fc1, m->dx, nullptr, &L.mlp_ln, nullptr, m->dh16, nullptr, R, WQ4_EPI_GELU, none, st));
             CHK(lin_sk(L.fc2, nullptr, m->dh16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
@@ -628,7 +628,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         CHK(lin_n(L.cq, m->dq, nullptr, 0));
         if (q_len == 1 && m->da_part)
             CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, f16p ? m->datt16 : nullptr, D, B, H,
-                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1));
         else
             CHK(wq4m_dec_attention(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, D, B, H, q_len, m->T_enc, -1, st));
         CHK(lin_att(L.cout));
