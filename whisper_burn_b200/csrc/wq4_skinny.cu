@@ -164,6 +164,17 @@ __global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const 
         __syncthreads();
     }
 
+    // bias and residual of the first output this thread will finish (the only one up to 16 rows), requested before the
+    // weight stream so that the epilogue has no dependent global load
+    float pre_b = 0.0f, pre_r = 0.0f;
+    if (tid < kSRows * p.rows) {
+        const int nn = row0 + (tid & (kSRows - 1));
+        if (nn < p.n) {
+            if (p.bias) pre_b = __ldg(p.bias + nn);
+            if (p.residual) pre_r = p.residual[(size_t)(tid >> 4) * p.ldy + nn];
+        }
+    }
+
     float acc[NT][4];
 #pragma unroll
     for (int j = 0; j < NT; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0f;
@@ -249,10 +260,11 @@ __global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const 
         if (nn >= p.n) continue;
         float s = 0.0f;
         for (int w2 = 0; w2 < kSW; w2++) s += red[w2 * (kSRows * RP) + r * RP + m];      // fixed order
-        if (p.bias) s += __ldg(p.bias + nn);
+        const bool first = o == tid;
+        if (p.bias) s += first ? pre_b : __ldg(p.bias + nn);
         if (p.flags & WQ4_EPI_GELU) s = wq4_gelu_tanh(s);
         const size_t oi = (size_t)m * p.ldy + nn;
-        if (p.residual) s += p.residual[oi];
+        if (p.residual) s += first ? pre_r : p.residual[oi];
         if (p.y32) p.y32[oi] = s;
         if (p.y16) p.y16[oi] = __ushort_as_half(f2h_sat(s));
         if (p.kc && nn >= p.kvD) {
