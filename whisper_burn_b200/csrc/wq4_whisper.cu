@@ -403,7 +403,7 @@ int32_t reserve(wq4_whisper *m, int64_t B)
         m->Vp = (m->V + 31) / 32 * 32;
         CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
         CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
-        if (B > 2) {   // batches beyond the single-kernel step take the per-op path
+        if (B > 1) {   // batches beyond the single-kernel step take the per-op path
             m->Vp256 = (m->V + 255) / 256 * 256;
             CHK(dev_alloc(m, &m->tok_emb16, (size_t)m->Vp256 * D));
             WQ4_CUDA(cudaMemset(m->tok_emb16, 0, (size_t)m->Vp256 * D * 2));
@@ -524,23 +524,23 @@ static bool use_decode_kernel()
 // offset, and the kernel takes the layer stride (kv_clips) separately from its own batch.
 constexpr int64_t kDecodeGroup = 8;
 // Largest batch that runs through the single-kernel step (in groups of 8 when an override allows more).  Measured
-// (profiles/r01_decode_step.txt): the persistent kernel wins at 1 and 2 clips (1.49 / 1.84 ms against 1.99 ms at 2); from 3
-// clips on the per-op path -- skinny linear with fused LayerNorm and cache append, key-per-lane attention kernel, 8 launches
-// per layer -- is faster (2.02 against 2.06 ms at 3, 2.04 against 2.29 ms at 4, 2.40 against 3.04 ms at 8), so the default
-// is 2; WQ4_DECODE_GROUP_MAX overrides it (tests).
+// (profiles/r01_decode_step.txt): the persistent kernel wins for a single clip (1.48 ms against ~1.7 ms); from 2 clips on
+// the per-op path -- skinny linear with fused LayerNorm and cache append, weights prefetched under the previous kernel,
+// key-per-lane attention kernel, 8 launches per layer -- is faster (1.76 against 1.84 ms at 2, 1.82 against 2.29 ms at 4,
+// 2.17 against 3.04 ms at 8), so the default is 1; WQ4_DECODE_GROUP_MAX overrides it (tests).
 // Smallest row count of the per-op path that runs on f16 operands (skinny linear / tcgen05 GEMM); below it the f32 GEMV.
 // WQ4_DECODE_F16_MIN overrides it (tuning runs together with WQ4_DECODE_GROUP_MAX).
 static int64_t decode_f16_min_rows()
 {
     static int64_t v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_DECODE_F16_MIN"); v = e ? atoll(e) : 3; if (v < 1) v = 1; }
+    if (v < 0) { const char *e = getenv("WQ4_DECODE_F16_MIN"); v = e ? atoll(e) : 2; if (v < 1) v = 1; }
     return v;
 }
 
 static int64_t decode_grouped_max()
 {
     static int64_t v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); v = e ? atoll(e) : 2; if (v < 1) v = 1; }
+    if (v < 0) { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); v = e ? atoll(e) : 1; if (v < 1) v = 1; }
     return v;
 }
 
