@@ -23,6 +23,8 @@
 // Large-V3) + f16 cross K/V + f16 self K/V + the f16 logits matrix; bench: scripts/bench_decode.py.
 #include <cooperative_groups.h>
 #include <float.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include "wq4_common.cuh"
 #include "wq4_model.cuh"
@@ -1252,8 +1254,25 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
     if (ns > 8) ns = 8;
     while (ns > 1 && (kv_len + ns - 1) / ns < 128) ns--;
     while (ns > 1 && units * ns * kPartStride > part_floats) ns--;
-    const int64_t keys_per_cta = (kv_len + ns - 1) / ns;
-    const bool wide = keys_per_cta > 512;
+    int64_t keys_per_cta = (kv_len + ns - 1) / ns;
+    bool wide = keys_per_cta > 512;
+    {   // tuning overrides: WQ4_DA_CROSS / WQ4_DA_SELF = "<splits>,<0|1 wide>" (kv_len > 512 counts as cross)
+        static int o_ns[2] = {-1, -1}, o_w[2] = {-1, -1};
+        static bool read = false;
+        if (!read) {
+            const char *e0 = getenv("WQ4_DA_SELF"), *e1 = getenv("WQ4_DA_CROSS");
+            if (e0) sscanf(e0, "%d,%d", &o_ns[0], &o_w[0]);
+            if (e1) sscanf(e1, "%d,%d", &o_ns[1], &o_w[1]);
+            read = true;
+        }
+        const int c = kv_len > 512 ? 1 : 0;
+        if (o_ns[c] > 0) {
+            ns = o_ns[c];
+            while (ns > 1 && units * ns * kPartStride > part_floats) ns--;
+            keys_per_cta = (kv_len + ns - 1) / ns;
+        }
+        if (o_w[c] >= 0) wide = o_w[c] != 0;
+    }
     static bool configured[64] = {};
     if (!configured[device & 63]) {
         WQ4_CUDA(cudaFuncSetAttribute(dec_attention_split_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)da_smem(8)));

@@ -19,6 +19,8 @@
 //   * cross-warp reduction of the K split in shared memory in a fixed order (deterministic), then bias -> GELU -> +residual
 //     -> f32 / f16 stores, and optionally the K/V rows of a fused q|k|v projection appended to the f16 self-attention
 //     cache in place (attention.rs:106-113 without the realloc), which removes the separate append launch.
+//   * launch chain: griddepcontrol.launch_dependents first, then the warp's weight blocks are prefetched into L2 BEFORE
+//     griddepcontrol.wait (weights do not depend on the previous kernel), bias / residual are requested before the weight loop.
 // Operand precision is that of the tensor-core GEMM (f16 operands, f32 accumulate).
 // XMODE 0: x is f16 [rows][K];  1: x is f32 (converted on load);  2: x is f32 and LayerNorm (layers.rs:23-31: biased
 // variance, eps 1e-5) is applied on load -- every CTA derives the row statistics itself (rows*K*4 bytes out of L2), which
