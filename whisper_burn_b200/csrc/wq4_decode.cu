@@ -1247,15 +1247,16 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
     const int64_t units = B * H;
     if (units < 1 || kv_len < 1) return WQ4_OK;
     const int sms = wq4_sm_count(device);
-    // Split only to fill the machine (two resident CTAs per SM): a split costs the partial write, a fence, an atomic and the
-    // merge by the last arriver, which a short self-attention row does not win back (measured: 15 -> 23 us at 225 keys
-    // when 640 units were split in two).
-    int64_t ns = (2 * (int64_t)sms + units - 1) / units;
+    // Split the keys only when there are fewer units than half the SMs: a split costs the partial write, a fence, an atomic
+    // and the merge by the last arriver.  Measured (scripts/sweep_da.sh, Large-V3 step): 80 units x 1500 keys unsplit on the
+    // 8-warp kernel 1.75 ms per step against 1.82 ms split in four and 1.91 ms in eight; 320 units unsplit 2.58 ms against
+    // 2.76-2.91 ms split; a 225-key self-attention row split in two costs 15 -> 23 us.
+    int64_t ns = ((int64_t)sms / 2 + units - 1) / units;
     if (ns > 8) ns = 8;
     while (ns > 1 && (kv_len + ns - 1) / ns < 128) ns--;
     while (ns > 1 && units * ns * kPartStride > part_floats) ns--;
     int64_t keys_per_cta = (kv_len + ns - 1) / ns;
-    bool wide = keys_per_cta > 512;
+    bool wide = keys_per_cta > 512 || units * ns <= sms;      // few units: eight warps per unit even on short rows
     {   // tuning overrides: WQ4_DA_CROSS / WQ4_DA_SELF = "<splits>,<0|1 wide>" (kv_len > 512 counts as cross)
         static int o_ns[2] = {-1, -1}, o_w[2] = {-1, -1};
         static bool read = false;
