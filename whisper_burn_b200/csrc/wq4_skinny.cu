@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const 
     }
 
     const size_t slab = (size_t)panel * p.kbp;
-#pragma unroll(NT == 2 ? 4 : (NT == 4 ? 2 : 1))
+#pragma unroll(NT <= 2 ? 4 : (NT == 4 ? 2 : 1))
     for (int kbi = warp; kbi < p.kb; kbi += kSW) {
         const uint32_t *wp = reinterpret_cast<const uint32_t *>(p.nib + (slab + kbi) * WQ4_PANEL_ROWS + rin);
         const uint32_t w_lo = ldg_nc32(wp + lane);            // rows g     (lane = 4g + t: word t of row g)
@@ -322,7 +322,8 @@ int32_t wq4_launch_skinny(const LinearArgs &a, const SkinnyExtra *ex)
     const unsigned grid = (unsigned)((w->n + kSRows - 1) / kSRows);
     WqProfScope prof(WQ4_PROF_GEMM_Q4, 2.0 * (double)a.rows * (double)w->n * (double)w->k, a.stream);
     int32_t st;
-    if (a.rows <= 16) st = launch_nt<2>(p, mode, grid, a.stream);
+    if (a.rows <= 8) st = launch_nt<1>(p, mode, grid, a.stream);
+    else if (a.rows <= 16) st = launch_nt<2>(p, mode, grid, a.stream);
     else if (a.rows <= 32) st = launch_nt<4>(p, mode, grid, a.stream);
     else st = launch_nt<8>(p, mode, grid, a.stream);
     if (st != WQ4_OK) return st;
