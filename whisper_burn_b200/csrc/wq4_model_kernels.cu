@@ -2,6 +2,7 @@
 // (SURVEY 8f "next" rows): LayerNorm, encoder self-attention, decoder attention over the KV caches,
 // embedding, log-mel transpose, argmax.  All emit the 16-bit operand the next GEMM consumes so no
 // separate conversion pass exists.
+#include <cooperative_groups.h>
 #include <float.h>
 
 #include <cstdlib>
@@ -513,6 +514,60 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ 
     if (threadIdx.x == 0) out[b] = si[0];
 }
 
+// The same pick (whisper.rs:131-138: the LAST maximum wins, `suppress` excluded) by a cluster of kArgCluster CTAs per row:
+// every CTA scans a contiguous eighth of [lo, hi), rank 0 merges the eight (value, index) partials through distributed
+// shared memory in rank order (ascending index ranges, ">=": the later one wins ties).
+constexpr int kArgCluster = 8;
+__global__ void __launch_bounds__(256) argmax_cluster_kernel(const float *__restrict__ logits, int V, int lo, int hi,
+                                                             const int *__restrict__ suppress, int *__restrict__ out)
+{
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int b = blockIdx.y, rank = (int)cluster.block_rank();
+    const float *lg = logits + (size_t)b * V;
+    const int sup = suppress ? suppress[b] : -1;
+    const int per = (hi - lo + kArgCluster - 1) / kArgCluster;
+    const int c0 = lo + rank * per, c1 = min(hi, c0 + per);
+    float best = -INFINITY;
+    int bi = -1;
+    for (int i = c0 + threadIdx.x; i < c1; i += 256) {
+        const float v = (i == sup) ? -INFINITY : lg[i];
+        if (bi < 0 || v >= best) { best = v; bi = i; }
+    }
+    // warp: keep the larger value, the larger index on ties
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (oi >= 0 && (bi < 0 || ov > best || (ov == best && oi > bi))) { best = ov; bi = oi; }
+    }
+    __shared__ float sv[8];
+    __shared__ int si[8];
+    __shared__ float cv;
+    __shared__ int ci;
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float mv = -INFINITY;
+        int mi = -1;
+        for (int w = 0; w < 8; w++)
+            if (si[w] >= 0 && (mi < 0 || sv[w] > mv || (sv[w] == mv && si[w] > mi))) { mv = sv[w]; mi = si[w]; }
+        cv = mv; ci = mi;
+    }
+    cluster.sync();
+    if (rank == 0 && threadIdx.x == 0) {
+        float mv = -INFINITY;
+        int mi = -1;
+        for (int r = 0; r < kArgCluster; r++) {
+            const float rv = *cluster.map_shared_rank(&cv, r);
+            const int ri = *cluster.map_shared_rank(&ci, r);
+            if (ri >= 0 && (mi < 0 || rv > mv || (rv == mv && ri > mi))) { mv = rv; mi = ri; }
+        }
+        out[b] = mi;
+    }
+    cluster.sync();      // keep every rank's shared memory alive until rank 0 has read it
+}
+
 // f32 [rows][D] -> f16 K/V cache rows (self-attention cache append, attention.rs:106-113 without the realloc)
 __global__ void kv_append_kernel(const float *__restrict__ kv, int ld_src, __half *__restrict__ kc, __half *__restrict__ vc,
                                  int ldkv, long long kv_batch_stride, int D, int q_len, int pos0)
@@ -666,6 +721,21 @@ int32_t wq4m_logits(const float *x, const float *emb, float *logits, int64_t nb,
 int32_t wq4m_argmax(const float *logits, int64_t nb, int64_t V, int64_t lo, int64_t hi, const int *suppress, int *out,
                     cudaStream_t st)
 {
+    if (hi - lo >= 8192) {
+        // whole-vocabulary pick: a cluster of eight CTAs per row (one CTA per row spends ~30 us on 51 866 logits)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(kArgCluster, (unsigned)nb, 1);
+        cfg.blockDim = dim3(256, 1, 1);
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = kArgCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        WQ4_CUDA(cudaLaunchKernelEx(&cfg, argmax_cluster_kernel, logits, (int)V, (int)lo, (int)hi, suppress, out));
+        wq4_count_launch();
+        return WQ4_OK;
+    }
     argmax_kernel<<<(unsigned)nb, 1024, 0, st>>>(logits, (int)V, (int)lo, (int)hi, suppress, out);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
