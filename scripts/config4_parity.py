@@ -30,6 +30,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seed", type=int, default=2)
     ap.add_argument("--modes", default="en,auto")
+    ap.add_argument("--batch-check", type=int, default=0,
+                    help="also compare teacher-forced decode logits of a batch of N clips (test.wav + synthetic mels) with the "
+                         "oracle clip by clip: the per-op decode path (skinny linear, key-per-lane attention) at full size")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     t0 = time.time()
@@ -39,7 +42,7 @@ def main():
     q4.set_threads(q4.host_cores())
     oracle = wn.WhisperOracle(blob, cfg)
     model = wb.load_whisper_from_gguf(blob, wb.WhisperConfig.large_v3(), dev)
-    model.reserve(1)
+    model.reserve(max(1, a.batch_check))        # buffers are sized once
     g = np.load(ROOT / "tests" / "golden" / "test_wav_mel.npz")
     mel = np.ascontiguousarray(g["mel128"][None]).astype(np.float32)
     mel_d = torch.from_numpy(mel).to(dev)
@@ -75,6 +78,29 @@ def main():
                               "first_difference_at": first_diff, "distinct_tokens": len(set(want[:n])),
                               "first_tokens": want[:8], "oracle_seconds": round(dt, 1)}
         print(mode, json.dumps(out["modes"][mode]), flush=True)
+    if a.batch_check > 0:
+        nb = a.batch_check
+        mels = np.concatenate([mel] + [wn.synthetic_mel(1, cfg.n_mels, 3000, seed=300 + i) for i in range(nb - 1)], axis=0)
+        model.encode(torch.from_numpy(mels).to(dev), want_output=False)
+        encs = [enc_want] + [oracle.encode(mels[b:b + 1]) for b in range(1, nb)]
+        caches = [oracle.new_cache() for _ in range(nb)]
+        prompts = [[wn.SOT, 50259 + b, cfg.transcribe_token(), cfg.no_timestamps_token()] for b in range(nb)]
+        want = [oracle.forward_prompt(prompts[b], encs[b], caches[b]) for b in range(nb)]
+        got = model.decoder_pass(prompts, 0, 0, recompute_cross=True).cpu().numpy()
+        rel = lambda x, y: float(np.abs(x - y).max() / np.abs(y).max())
+        worst = max(rel(got[b], want[b]) for b in range(nb))
+        same = all(int(got[b].argmax()) == int(want[b].argmax()) for b in range(nb))
+        toks, pos = [int(w.argmax()) for w in want], 4
+        for step in range(8):
+            want = [oracle.decode_step(toks[b], pos, encs[b], caches[b]) for b in range(nb)]
+            got = model.decoder_pass([[t] for t in toks], pos, pos).cpu().numpy()
+            worst = max(worst, max(rel(got[b], want[b]) for b in range(nb)))
+            same = same and all(int(got[b].argmax()) == int(want[b].argmax()) for b in range(nb))
+            toks = [(int(w.argmax()) + 17 * b) % 50000 for b, w in enumerate(want)]     # distinct per clip, deterministic
+            pos += 1
+        out["batch_check"] = {"clips": nb, "steps": 9, "worst_logit_rel_err": worst, "argmax_identical": bool(same)}
+        print("batch", json.dumps(out["batch_check"]), flush=True)
+        ok_all = ok_all and worst < 1e-2
     out["pass"] = bool(ok_all)
     print(json.dumps(out))
     assert wb.lib().wq4_device_error_flag(0) == 0
