@@ -89,18 +89,30 @@ def main():
         got = model.decoder_pass(prompts, 0, 0, recompute_cross=True).cpu().numpy()
         rel = lambda x, y: float(np.abs(x - y).max() / np.abs(y).max())
         worst = max(rel(got[b], want[b]) for b in range(nb))
-        same = all(int(got[b].argmax()) == int(want[b].argmax()) for b in range(nb))
+        mism = []          # (relative top-1/top-2 margin of the ORACLE, relative logit error) where the arg-max differs
+
+        def note(g, w):
+            if int(g.argmax()) != int(w.argmax()):
+                s2 = np.partition(w, -2)[-2:]
+                mism.append((float((s2[1] - s2[0]) / np.abs(w).max()), rel(g, w)))
+        for b in range(nb):
+            note(got[b], want[b])
         toks, pos = [int(w.argmax()) for w in want], 4
         for step in range(8):
             want = [oracle.decode_step(toks[b], pos, encs[b], caches[b]) for b in range(nb)]
             got = model.decoder_pass([[t] for t in toks], pos, pos).cpu().numpy()
             worst = max(worst, max(rel(got[b], want[b]) for b in range(nb)))
-            same = same and all(int(got[b].argmax()) == int(want[b].argmax()) for b in range(nb))
+            for b in range(nb):
+                note(got[b], want[b])
             toks = [(int(w.argmax()) + 17 * b) % 50000 for b, w in enumerate(want)]     # distinct per clip, deterministic
             pos += 1
-        out["batch_check"] = {"clips": nb, "steps": 9, "worst_logit_rel_err": worst, "argmax_identical": bool(same)}
+        # an arg-max may only differ where the oracle's own decision margin is inside the numeric error of the logits
+        explained = all(m <= 2.0 * e for m, e in mism)
+        out["batch_check"] = {"clips": nb, "steps": 9, "worst_logit_rel_err": worst, "argmax_compared": nb * 9,
+                              "argmax_different": len(mism), "largest_oracle_margin_where_different": max([m for m, _ in mism], default=0.0),
+                              "differences_within_error": bool(explained)}
         print("batch", json.dumps(out["batch_check"]), flush=True)
-        ok_all = ok_all and worst < 1e-2
+        ok_all = ok_all and worst < 1e-2 and explained
     out["pass"] = bool(ok_all)
     print(json.dumps(out))
     assert wb.lib().wq4_device_error_flag(0) == 0
