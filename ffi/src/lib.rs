@@ -144,3 +144,111 @@ impl Conv1D {
 impl Drop for Conv1D {
     fn drop(&mut self) { unsafe { sys::wq4_conv1d_destroy(self.raw); } }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Model level: the reference's names for the callers of the Q4 path, over the batched C ABI.
+// ---------------------------------------------------------------------------------------------
+
+/// Whisper token budget of one transcription (src/model/whisper.rs:20).
+pub const MAX_TOKENS: usize = 224;
+
+/// `WhisperConfig` (src/model/config.rs:5-28); `large_v3()` / `medium()` as config.rs:32-63.
+pub type WhisperConfig = sys::wq4_whisper_config;
+
+pub fn whisper_config(preset: &str) -> Result<WhisperConfig> {
+    let name = std::ffi::CString::new(preset)?;
+    let mut cfg: WhisperConfig = unsafe { std::mem::zeroed() };
+    if unsafe { sys::wq4_whisper_config_preset(name.as_ptr(), &mut cfg) } != sys::WQ4_OK {
+        bail!("{}", last_error());
+    }
+    Ok(cfg)
+}
+
+/// `WhisperModel` (src/model/whisper.rs:22-128): encoder + decoder with in-place f16 KV caches, batched.
+pub struct WhisperModel {
+    raw: *mut sys::wq4_whisper,
+}
+unsafe impl Send for WhisperModel {}
+
+impl WhisperModel {
+    /// `load_whisper_from_gguf` (src/gguf/loader.rs:26-46): the file is mapped and uploaded tensor by tensor.
+    pub fn load_from_gguf(path: &std::path::Path, config: &WhisperConfig, device: i32) -> Result<Self> {
+        let p = std::ffi::CString::new(path.to_string_lossy().as_bytes())?;
+        let mut out = ptr::null_mut();
+        if unsafe { sys::wq4_whisper_load_gguf(p.as_ptr(), config, device, &mut out) } != sys::WQ4_OK {
+            bail!("Failed to load GGUF model: {}", last_error());
+        }
+        Ok(Self { raw: out })
+    }
+    /// `encode` (whisper.rs:41-43): mel `[B, n_mels, 3000]` on the device -> `[B, 1500, D]` (optional copy out).
+    pub fn encode(&self, mel_dev: *const f32, batch: usize, enc_out_dev: *mut f32, stream: sys::wq4_stream) {
+        expect_ok(unsafe { sys::wq4_whisper_encode(self.raw, mel_dev, batch as i64, enc_out_dev, stream) }, "encode");
+    }
+    /// `transcribe` (whisper.rs:51-128) for a batch of clips; `lang` = language token per clip, `None` = auto-detect
+    /// (one mode per call).  Returns the generated ids per clip.
+    pub fn transcribe(&self, mel_dev: *const f32, batch: usize, lang: Option<&[i32]>, stream: sys::wq4_stream) -> Vec<Vec<i32>> {
+        let langs: Vec<i32> = match lang { Some(l) => l.to_vec(), None => vec![-1; batch] };
+        let mut toks = vec![0i32; batch * MAX_TOKENS];
+        let mut counts = vec![0i32; batch];
+        expect_ok(unsafe {
+            sys::wq4_whisper_transcribe(self.raw, mel_dev, batch as i64, langs.as_ptr(), toks.as_mut_ptr(),
+                                        counts.as_mut_ptr(), ptr::null_mut(), stream)
+        }, "transcribe");
+        (0..batch).map(|b| toks[b * MAX_TOKENS..b * MAX_TOKENS + counts[b] as usize].to_vec()).collect()
+    }
+    pub fn as_ptr(&self) -> *mut sys::wq4_whisper { self.raw }
+}
+impl Drop for WhisperModel {
+    fn drop(&mut self) { unsafe { sys::wq4_whisper_destroy(self.raw); } }
+}
+
+/// `MelSpectrogram` (src/audio/mel.rs:45-157) on the device, batched.
+pub struct MelSpectrogram {
+    raw: *mut sys::wq4_logmel,
+}
+unsafe impl Send for MelSpectrogram {}
+impl MelSpectrogram {
+    pub fn new(n_mels: usize, device: i32, stream: sys::wq4_stream) -> Result<Self> {
+        let mut out = ptr::null_mut();
+        if unsafe { sys::wq4_logmel_create(n_mels as i32, device, stream, &mut out) } != sys::WQ4_OK {
+            bail!("{}", last_error());
+        }
+        Ok(Self { raw: out })
+    }
+    pub fn as_ptr(&self) -> *const sys::wq4_logmel { self.raw }
+}
+impl Drop for MelSpectrogram {
+    fn drop(&mut self) { unsafe { sys::wq4_logmel_destroy(self.raw); } }
+}
+
+/// `InferenceState` (src/transcribe.rs:26-31); the tokenizer stays with the caller.
+pub struct InferenceState {
+    pub model: WhisperModel,
+    pub mel: MelSpectrogram,
+    pub device: i32,
+    pub n_mels: usize,
+}
+
+/// `transcribe` (src/transcribe.rs:34-107) for a batch of utterances already resampled to 16 kHz and resident on the
+/// device: clip `b` = `pcm_dev[b*pcm_stride ..][..n_samples[b]]`.  Returns the text-token ids per clip (ids >= 50257
+/// dropped, :96-100) and the inference time in ms (:84-87); the caller runs `tokenizer.decode` (:102-105).
+pub fn transcribe(state: &InferenceState, pcm_dev: *const f32, pcm_stride: usize, n_samples: &[i64], language: Option<&[i32]>,
+                  stream: sys::wq4_stream) -> Result<(Vec<Vec<u32>>, u128)> {
+    let batch = n_samples.len();
+    let langs: Vec<i32> = match language { Some(l) => l.to_vec(), None => vec![-1; batch] };
+    let mut text = vec![0i32; batch * MAX_TOKENS];
+    let mut counts = vec![0i32; batch];
+    let mut ms = 0f64;
+    let st = unsafe {
+        sys::wq4_transcribe(state.model.as_ptr(), state.mel.as_ptr(), pcm_dev, pcm_stride as i64, n_samples.as_ptr(),
+                            batch as i64, langs.as_ptr(), text.as_mut_ptr(), counts.as_mut_ptr(), ptr::null_mut(),
+                            ptr::null_mut(), &mut ms, stream)
+    };
+    if st != sys::WQ4_OK {
+        bail!("{}", last_error());
+    }
+    let ids = (0..batch)
+        .map(|b| text[b * MAX_TOKENS..b * MAX_TOKENS + counts[b] as usize].iter().map(|&t| t as u32).collect())
+        .collect();
+    Ok((ids, ms as u128))
+}

@@ -88,6 +88,13 @@ extern "C" {
     pub fn wq4_logmel_forward(m: *const wq4_logmel, pcm_dev: *const f32, batch: i64, n_samples: i64,
                               mel_dev: *mut f32, stream: wq4_stream) -> i32;
 
+    pub fn wq4_logmel_forward_ragged(m: *const wq4_logmel, pcm_dev: *const f32, batch: i64, stride: i64,
+                                     lens_dev: *const i64, mel_dev: *mut f32, stream: wq4_stream) -> i32;
+    pub fn wq4_transcribe(m: *mut wq4_whisper, mel: *const wq4_logmel, pcm_dev: *const f32, pcm_stride: i64,
+                          n_samples: *const i64, batch: i64, language: *const i32, text_tokens_out: *mut i32,
+                          text_counts_out: *mut i32, raw_tokens_out: *mut i32, raw_counts_out: *mut i32,
+                          elapsed_ms_out: *mut f64, stream: wq4_stream) -> i32;
+
     pub fn wq4_gguf_probe(data: *const u8, nbytes: usize, version: *mut u32, tensor_count: *mut u64,
                           data_offset: *mut u64) -> i32;
     pub fn wq4_gguf_tensor_info(data: *const u8, nbytes: usize, name: *const c_char, dims4: *mut u64,
@@ -106,9 +113,14 @@ extern "C" {
     pub fn wq4_whisper_transcribe(m: *mut wq4_whisper, mel_dev: *const f32, batch: i64, lang_tokens: *const i32,
                                   tokens_out: *mut i32, counts_out: *mut i32, detected_lang_out: *mut i32,
                                   stream: wq4_stream) -> i32;
+    pub fn wq4_whisper_transcribe_ex(m: *mut wq4_whisper, mel_dev: *const f32, batch: i64, lang_tokens: *const i32,
+                                     max_new_tokens: *const i32, tokens_out: *mut i32, counts_out: *mut i32,
+                                     detected_lang_out: *mut i32, stream: wq4_stream) -> i32;
     pub fn wq4_whisper_decoder_pass(m: *mut wq4_whisper, tokens_host: *const i32, batch: i64, q_len: i64,
                                     emb_pos0: i64, kv_pos0: i64, recompute_cross: i32, logits_dev: *mut f32,
                                     stream: wq4_stream) -> i32;
+    pub fn wq4_whisper_decoder_pass_slots(m: *mut wq4_whisper, tokens_host: *const i32, slots_host: *const i32, rows: i64,
+                                          emb_pos: i64, kv_pos: i64, logits_dev: *mut f32, stream: wq4_stream) -> i32;
     pub fn wq4_whisper_decode_step_device(m: *mut wq4_whisper, batch: i64, position: i64, kv_len: i64,
                                           stream: wq4_stream) -> i32;
 

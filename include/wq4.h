@@ -14,6 +14,8 @@
  *   wq4_whisper_load_gguf     load_whisper_from_gguf           src/gguf/loader.rs:26-46 (+ reader.rs:98-223)
  *   wq4_whisper_encode        WhisperModel::encode             src/model/whisper.rs:41, encoder.rs:87-115
  *   wq4_whisper_transcribe    WhisperModel::transcribe         src/model/whisper.rs:51-128 (batched; transcribe.rs:84-87)
+ *   wq4_transcribe            transcribe                       src/transcribe.rs:34-107 (samples -> text-token ids, batched)
+ *   wq4_logmel_forward        MelSpectrogram::compute_log      src/audio/mel.rs:105-157 (+ framing of transcribe.rs:46-82)
  *
  * Conventions
  *   - extern "C", plain pointers and sizes, int32_t status (0 = WQ4_OK).  Nothing aborts or
@@ -159,7 +161,8 @@ WQ4_API int32_t wq4_whisper_load_gguf_memory(const uint8_t *data, size_t nbytes,
                                              const wq4_whisper_config *cfg, int32_t device,
                                              wq4_whisper **out);
 WQ4_API int32_t wq4_whisper_destroy(wq4_whisper *m);
-/* Allocates activation / KV-cache workspaces for up to max_batch clips (once, before first use). */
+/* Allocates activation / KV-cache workspaces for up to max_batch clips.  Optional: encode / transcribe reserve what they need.
+ * A request above the current reservation synchronises the device and re-allocates (cache contents are not kept). */
 WQ4_API int32_t wq4_whisper_reserve(wq4_whisper *m, int64_t max_batch);
 WQ4_API int32_t wq4_whisper_info(const wq4_whisper *m, int64_t *d_model, int64_t *ffn, int64_t *vocab,
                                  int64_t *weight_bytes);
@@ -174,11 +177,22 @@ WQ4_API int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int
                                        const int32_t *lang_tokens, int32_t *tokens_out,
                                        int32_t *counts_out, int32_t *detected_lang_out,
                                        wq4_stream stream);
+/* Same with a per-clip token budget (host, [batch], clamped to 224; NULL = the reference's MAX_TOKENS): a clip that hits EOT
+ * (whisper.rs:105-108) or its budget leaves the active set, the remaining rows are compacted on the device. */
+WQ4_API int32_t wq4_whisper_transcribe_ex(wq4_whisper *m, const float *mel_dev, int64_t batch,
+                                          const int32_t *lang_tokens, const int32_t *max_new_tokens,
+                                          int32_t *tokens_out, int32_t *counts_out, int32_t *detected_lang_out,
+                                          wq4_stream stream);
 /* One decoder pass over q_len new tokens per clip after wq4_whisper_encode (test / bench hook);
  * logits_dev [batch][vocab] of the last position (may be NULL). */
 WQ4_API int32_t wq4_whisper_decoder_pass(wq4_whisper *m, const int32_t *tokens_host, int64_t batch,
                                          int64_t q_len, int64_t emb_pos0, int64_t kv_pos0,
                                          int32_t recompute_cross, float *logits_dev, wq4_stream stream);
+/* One single-query step over a subset of the clips the caches hold: row r = clip slots_host[r] (test hook of the greedy
+ * loop's active-set compaction); logits_dev [rows][vocab]. */
+WQ4_API int32_t wq4_whisper_decoder_pass_slots(wq4_whisper *m, const int32_t *tokens_host, const int32_t *slots_host,
+                                               int64_t rows, int64_t emb_pos, int64_t kv_pos, float *logits_dev,
+                                               wq4_stream stream);
 /* Stream-ordered greedy decode step on device-resident tokens (CUDA-graph capturable). */
 WQ4_API int32_t wq4_whisper_decode_step_device(wq4_whisper *m, int64_t batch, int64_t position,
                                                int64_t kv_len, wq4_stream stream);
@@ -194,6 +208,19 @@ WQ4_API int32_t wq4_logmel_destroy(wq4_logmel *m);
 /* pcm_dev [batch][n_samples] f32, 16 kHz mono -> mel_dev [batch][n_mels][3000] f32 (the encoder's input). */
 WQ4_API int32_t wq4_logmel_forward(const wq4_logmel *m, const float *pcm_dev, int64_t batch,
                                    int64_t n_samples, float *mel_dev, wq4_stream stream);
+
+/* Ragged batch: clip b = pcm_dev[b*stride .. b*stride + lens_dev[b]) (lens_dev: DEVICE int64 [batch], each <= stride). */
+WQ4_API int32_t wq4_logmel_forward_ragged(const wq4_logmel *m, const float *pcm_dev, int64_t batch, int64_t stride,
+                                          const int64_t *lens_dev, float *mel_dev, wq4_stream stream);
+
+/* ---- transcribe (src/transcribe.rs:34-107) for a batch of utterances: 16 kHz mono f32 samples on the device ->
+ * pad/truncate to 30 s -> log-mel -> encoder -> greedy decode -> ids >= 50257 dropped.  n_samples, language (token per clip,
+ * < 0 = auto-detect, one mode per call) and every output are HOST arrays; text_tokens_out [batch][224], text_counts_out
+ * [batch]; raw_tokens_out / raw_counts_out / elapsed_ms_out may be NULL.  Synchronises `stream`. */
+WQ4_API int32_t wq4_transcribe(wq4_whisper *m, const wq4_logmel *mel, const float *pcm_dev, int64_t pcm_stride,
+                               const int64_t *n_samples, int64_t batch, const int32_t *language,
+                               int32_t *text_tokens_out, int32_t *text_counts_out, int32_t *raw_tokens_out,
+                               int32_t *raw_counts_out, double *elapsed_ms_out, wq4_stream stream);
 
 /* ---- Introspection used by bench.py / tests ------------------------------------------- */
 /* Which kernel family a [rows,K]x[N,K]^T call dispatches to: 0 = GEMV (CUDA cores),

@@ -225,13 +225,15 @@ class WhisperOracle:
         m = logits.max()
         return int(np.flatnonzero(logits == m)[-1])
 
-    def transcribe(self, mel, lang_token: int | None, enc=None, return_margins=False):   # whisper.rs:51-128
+    def transcribe(self, mel, lang_token: int | None, enc=None, return_margins=False, max_new_tokens=None):   # whisper.rs:51-128
+        # max_new_tokens: per-clip token budget <= MAX_TOKENS (a batching extension of the C ABI; None = the reference's 224)
         c = self.cfg
         if enc is None:
             enc = self.encode(mel)
         cache = self.new_cache()
         position = 0
         margins = []
+        self.last_maxabs = []            # max |logit| of every step whose margin is recorded (same order as margins)
         if lang_token is not None:
             prompt = [SOT, lang_token, c.transcribe_token(), c.no_timestamps_token()]
         else:
@@ -242,19 +244,23 @@ class WhisperOracle:
             lang_token = rng_[0] + int(np.flatnonzero(sub == sub.max())[-1])  # max_by: last max
             s2 = np.sort(sub)
             margins.append(float(s2[-1] - s2[-2]))
+            self.last_maxabs.append(float(np.abs(logits).max()))
             prompt = [lang_token, c.transcribe_token(), c.no_timestamps_token()]
         logits = self.forward_prompt(prompt, enc, cache)
         position += len(prompt)
         logits[EOT] = -np.inf
         nxt = self.argmax(logits)
         generated = []
-        for step in range(MAX_TOKENS):
-            s2 = np.partition(logits[np.isfinite(logits)], -2)[-2:]
+        limit = MAX_TOKENS if max_new_tokens is None else max(0, min(MAX_TOKENS, int(max_new_tokens)))
+        for step in range(limit):
+            fin = logits[np.isfinite(logits)]
+            s2 = np.partition(fin, -2)[-2:]
             margins.append(float(s2[1] - s2[0]))
+            self.last_maxabs.append(float(np.abs(fin).max()))
             if nxt == EOT:
                 break
             generated.append(nxt)
-            if step == MAX_TOKENS - 1:
+            if step == limit - 1:
                 break
             logits = self.decode_step(nxt, position, enc, cache)
             position += 1
@@ -321,6 +327,68 @@ def random_state(cfg: WhisperConfig, seed: int, n_vocab: int = 51866, lin_std=0.
     return st
 
 
+# ------------------------------------------------------------------------------------------------
+# "Walk" embeddings: a random-init model whose greedy path is NOT a fixed point.
+#
+# With plain random weights the residual stream carries token_embedding[tok] straight into the tied logits matrix, so
+# arg-max = the input token and a 224-token transcription is one token repeated (round-1 finding).  Here the token and
+# positional embeddings carry a 16-bit code on a few blocks of coordinates (on top of the random part the layers see):
+#   token v < 2^15            : code = the bits of v, "special" bit (bit 15) = -1
+#   token v >= 2^15 (specials): code = the bits of v - 2^15, special bit = +1
+#   position p                : +-2 on a position-dependent subset of the 15 code bits ("forced"), 0 on the others
+#                               ("copied" from the previous token), -2 on the special bit
+# The final LayerNorm keeps signs, so logit_w ~ sum_i s_i * code_i(w) with s = code(prev token) + code(position): the
+# winner is the token whose bits are sign(s), i.e. every bit is either forced by the position or copied from the
+# previous token.  The greedy path therefore walks the vocabulary, depends on the fed-back token at every step (a wrong
+# token breaks the copied bits), never lands on an id >= 2^15 (so never on EOT unless `eot_alias_step` asks for it),
+# and the top-1 / top-2 margin is 2*min|s_i| out of sum|s_i| -- several per cent of the largest logit, far above the
+# 1e-3 numeric error.  The 32 random layers still add their (audio-dependent) contribution to every coordinate; the code
+# amplitude `c` is chosen so that contribution is a perturbation of the margin, not its source.
+WALK_BITS = 15
+
+
+def _walk_code(ids):
+    ids = np.asarray(ids, dtype=np.int64)
+    special = ids >= (1 << WALK_BITS)
+    low = np.where(special, ids - (1 << WALK_BITS), ids)
+    bits = ((low[:, None] >> np.arange(WALK_BITS)[None, :]) & 1) * 2 - 1
+    return np.concatenate([bits, np.where(special, 1, -1)[:, None]], axis=1).astype(np.float32)   # [n, 16]
+
+
+def walk_position_codes(n_ctx: int, seed: int, forced_frac: float = 0.6):
+    rng = np.random.default_rng(seed + 7919)
+    forced = rng.random((n_ctx, WALK_BITS)) < forced_frac
+    sign = rng.integers(0, 2, (n_ctx, WALK_BITS)) * 2 - 1
+    psi = np.where(forced, 2 * sign, 0)
+    return np.concatenate([psi, np.full((n_ctx, 1), -2)], axis=1).astype(np.float32)             # [ctx, 16]
+
+
+def walk_next(prev_token: int, position: int, psi) -> tuple[int, float]:
+    """The structural prediction: next token and (2*min|s|) / sum|s| for prev_token fed at `position`."""
+    s = _walk_code([prev_token])[0] + psi[position]
+    bits = (s[:WALK_BITS] > 0).astype(np.int64)
+    return int((bits << np.arange(WALK_BITS)).sum()), float(2 * np.abs(s).min() / np.abs(s).sum())
+
+
+def walk_embeddings(state: dict, cfg: WhisperConfig, seed: int, c: float = 100.0, eot_alias_token: int | None = None):
+    """Replaces decoder.token_embedding.weight / decoder.positional_embedding of `state` (in place) by their walk form.
+    eot_alias_token: a regular token id whose code EOT takes over (and which gets EOT's): the walk then ends there."""
+    tok = state["decoder.token_embedding.weight"]
+    pos = state["decoder.positional_embedding"]
+    n_vocab, D = tok.shape
+    nb = WALK_BITS + 1
+    bs = max(1, min(16, D // (2 * nb)))
+    amp = np.float32(c / np.sqrt(bs))
+    ids = np.arange(n_vocab)
+    if eot_alias_token is not None:
+        ids[EOT], ids[eot_alias_token] = eot_alias_token, EOT
+    code = _walk_code(ids)
+    psi = walk_position_codes(cfg.n_text_ctx, seed)
+    tok[:, :nb * bs] += np.repeat(code, bs, axis=1) * amp
+    pos[:, :nb * bs] += np.repeat(psi, bs, axis=1) * amp
+    return psi
+
+
 def should_quantize(name: str, shape) -> bool:      # scripts/convert_whisper.py:77-96
     if len(shape) != 2 or min(shape) < 256:
         return False
@@ -342,6 +410,37 @@ def state_to_gguf(state: dict) -> bytes:
             tensors.append((name, a.shape, gguf_np.GGML_F32, a.tobytes()))
     return gguf_np.write_gguf(tensors, metadata=[("general.architecture", 8, "whisper"),
                                                  ("general.name", 8, "random-init")])
+
+
+def state_to_tensors(state: dict):
+    q4.set_threads(q4.host_cores())
+    tensors = []
+    for name in sorted(state):
+        a = np.ascontiguousarray(state[name], dtype=np.float32)
+        if should_quantize(name, a.shape):
+            tensors.append((name, a.shape, gguf_np.GGML_Q4_0, q4.quantize_q4_0_converter(a).tobytes()))
+        else:
+            tensors.append((name, a.shape, gguf_np.GGML_F32, a.tobytes()))
+    return tensors
+
+
+def plain_and_walk_gguf(cfg: WhisperConfig, seed: int, eot_alias_token: int | None = None):
+    """Two checkpoints that share every weight except the two decoder embedding tables: the plain random-init model
+    (logits fully determined by the layers: the teacher-forced logits checks) and its walk form (token-parity checks).
+    Quantises once.  Returns (plain_gguf, walk_gguf, psi)."""
+    state = random_state(cfg, seed)
+    tensors = state_to_tensors(state)
+    meta = [("general.architecture", 8, "whisper"), ("general.name", 8, "random-init")]
+    plain = gguf_np.write_gguf(tensors, metadata=meta)
+    psi = walk_embeddings(state, cfg, seed, eot_alias_token=eot_alias_token)
+    swap = {n: np.ascontiguousarray(state[n], dtype=np.float32) for n in ("decoder.token_embedding.weight", "decoder.positional_embedding")}
+    tensors = [(n, sh, dt, swap[n].tobytes() if n in swap else raw) for n, sh, dt, raw in tensors]
+    return plain, gguf_np.write_gguf(tensors, metadata=meta), psi
+
+
+def teacher_token(clip: int, step: int) -> int:
+    """Deterministic, varied teacher-forced token for (clip, step) -- regular vocabulary ids only."""
+    return (1000 + 7919 * step + 2311 * clip + 17 * step * step) % 50000
 
 
 def tiny_config(d=256, heads=4, enc_layers=2, dec_layers=2, n_mels=80, n_lang=99, n_audio_ctx=1500):

@@ -78,7 +78,9 @@ def test_default_dispatch_and_determinism():
     t = wb.Q4Tensor.from_q4_bytes(qb, [n, k], DEV)
     L = wb.lib()
     tile = C.c_int32()
-    assert L.wq4_linear_plan(t._h, 8, 0, C.byref(tile)) == 0
+    assert L.wq4_linear_plan(t._h, 2, 0, C.byref(tile)) == 0            # 1-2 rows: f32 GEMV
+    assert L.wq4_linear_plan(t._h, 8, wb.WQ4_FORCE_GEMV, C.byref(tile)) == 0
+    assert L.wq4_linear_plan(t._h, 3, 0, C.byref(tile)) == 2 and tile.value == 16   # 3..16 rows: skinny kernel
     assert L.wq4_linear_plan(t._h, 9, 0, C.byref(tile)) == 2 and tile.value == 16
     assert L.wq4_linear_plan(t._h, 16, 0, C.byref(tile)) == 2
     assert L.wq4_linear_plan(t._h, 17, 0, C.byref(tile)) == 1          # beyond 16 rows the tcgen05 GEMM is faster

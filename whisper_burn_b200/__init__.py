@@ -8,5 +8,5 @@ from ._lib import Wq4Error, build, lib, launch_count, reset_launch_count  # noqa
 from ._lib import WQ4_EPI_GELU, WQ4_FORCE_GEMM, WQ4_FORCE_GEMV, WQ4_FORCE_SKINNY, WQ4_OPERANDS_BF16  # noqa: F401
 from .gguf import Q4Linear, Q4Tensor, q4_matmul  # noqa: F401
 from .layers import Conv1D, Q4FFN  # noqa: F401
-from .model import InferenceState, WhisperConfig, WhisperModel, lang_token, load_whisper_from_gguf, transcribe_mels  # noqa: F401
+from .model import InferenceState, WhisperConfig, WhisperModel, lang_token, load_whisper_from_gguf, transcribe, transcribe_mels  # noqa: F401
 from .audio import MelSpectrogram  # noqa: F401

@@ -82,6 +82,7 @@ def lib() -> C.CDLL:
     L.wq4_logmel_create.argtypes = [i32, i32, vp, C.POINTER(vp)]
     L.wq4_logmel_destroy.argtypes = [vp]
     L.wq4_logmel_forward.argtypes = [vp, vp, i64, i64, vp, vp]
+    L.wq4_logmel_forward_ragged.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     L.wq4_linear_plan.argtypes = [vp, i64, u32, C.POINTER(i32)]
     L.wq4_launch_count.restype = i64
     L.wq4_launch_count_reset.restype = None
@@ -92,7 +93,7 @@ def lib() -> C.CDLL:
                "wq4_tensor_dequantize", "wq4_tensor_export_gguf", "wq4_matmul", "wq4_linear_forward",
                "wq4_linear_forward_ex", "wq4_ffn_forward", "wq4_conv1d_create", "wq4_conv1d_destroy",
                "wq4_conv1d_forward", "wq4_linear_plan", "wq4_device_error_flag", "wq4_logmel_create",
-               "wq4_logmel_destroy", "wq4_logmel_forward"):
+               "wq4_logmel_destroy", "wq4_logmel_forward", "wq4_logmel_forward_ragged"):
         getattr(L, fn).restype = i32
     _lib = L
     return L

@@ -181,18 +181,13 @@ int32_t wq4_launch_cvt_f32_to_16(const float *src, void *dst, int64_t n, bool bf
 // ---- dispatch -----------------------------------------------------------------------------------
 bool wq4_pdl_enabled()
 {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_PDL"); v = (e && atoi(e) == 0) ? 0 : 1; }
-    return v != 0;
+    static const bool v = [] { const char *e = getenv("WQ4_PDL"); return !(e && atoi(e) == 0); }();   // thread-safe one-time read
+    return v;
 }
 
 int wq4_gemm_impl()
 {
-    static int impl = -1;
-    if (impl < 0) {
-        const char *e = getenv("WQ4_GEMM_IMPL");
-        impl = (e && atoi(e) == 1) ? 1 : 2;
-    }
+    static const int impl = [] { const char *e = getenv("WQ4_GEMM_IMPL"); return (e && atoi(e) == 1) ? 1 : 2; }();
     return impl;
 }
 
@@ -200,20 +195,21 @@ static bool use_gemv(int64_t rows, uint32_t flags, bool has_f32_x)
 {
     if (flags & WQ4_FORCE_GEMM) return false;
     if (!has_f32_x) return false;
-    return rows <= 8;
+    // 1-2 rows: f32 CUDA-core GEMV.  From 3 rows the mma.sync skinny kernel is faster (8 rows 1280 -> 5120: 15.9 us on the
+    // GEMV, whose cost grows with the row count, against ~5 us; profiles/r01_microbench_*.txt); WQ4_FORCE_GEMV keeps <= 8 rows here.
+    return rows <= (flags & WQ4_FORCE_SKINNY ? 0 : 2);
 }
 
-// 9..16 rows (up to 64 with WQ4_FORCE_SKINNY): the mma.sync skinny kernel (16 weight rows per CTA) instead of 256-row
+// 3..16 rows (up to 64 with WQ4_FORCE_SKINNY): the mma.sync skinny kernel (16 weight rows per CTA) instead of 256-row
 // tcgen05 tiles on a handful of SMs; beyond 16 rows the tcgen05 kernel is the faster one (wq4_skinny.cu header).
 // WQ4_SKINNY=0 in the environment restores the tcgen05 path for these row counts (A/B runs).
 static bool use_skinny(const wq4_tensor *w, int64_t rows, uint32_t flags)
 {
-    static int on = -1;
-    if (on < 0) { const char *e = getenv("WQ4_SKINNY"); on = (e && atoi(e) == 0) ? 0 : 1; }
+    static const bool on = [] { const char *e = getenv("WQ4_SKINNY"); return !(e && atoi(e) == 0); }();
     if (flags & (WQ4_FORCE_GEMM | WQ4_OPERANDS_BF16)) return false;
     if (!wq4_skinny_supported(w, rows)) return false;
     if (flags & WQ4_FORCE_SKINNY) return true;
-    return on && rows > 8 && rows <= WQ4_SKINNY_DEFAULT_ROWS;
+    return on && rows > 2 && rows <= WQ4_SKINNY_DEFAULT_ROWS;
 }
 
 static int32_t check_linear(const wq4_tensor *w, const char *who)

@@ -21,6 +21,8 @@
 #include <cstdlib>
 #include <mutex>
 
+#include <atomic>
+
 #include "wq4_common.cuh"
 #include "wq4_model.cuh"
 #include "wq4_ptx.cuh"
@@ -559,7 +561,7 @@ int32_t wq4m_enc_attention_tc(const void *qkv16, void *out16, int64_t B, int64_t
                       (long long)T, (long long)D, qkv16);
         return WQ4_ERR_CUDA;
     }
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];
     if (device < 0 || device >= 64 || !attr_done[device]) {
         WQ4_CUDA(cudaFuncSetAttribute(enc_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
         WQ4_CUDA(cudaFuncSetAttribute(enc_attention_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2SmemAlloc));

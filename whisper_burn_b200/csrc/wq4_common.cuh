@@ -125,6 +125,7 @@ struct SkinnyExtra {
     const float *ln_w, *ln_b;          // LayerNorm weight / bias over K, or null
     void *kc, *vc;                     // f16 caches [clip][ctx][kv_ld] or null; row m of x belongs to clip m
     int64_t kv_batch_stride, kv_ld, kv_pos, kv_d;
+    const int *kv_slot;                // device: cache slot of row m (active-set compaction of a decode batch), or null = m
 };
 int32_t wq4_launch_skinny(const LinearArgs &a, const SkinnyExtra *ex);
 bool wq4_skinny_supported(const wq4_tensor *w, int64_t rows);   // matrix-mode weight, 1..64 rows

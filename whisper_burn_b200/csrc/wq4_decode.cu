@@ -26,6 +26,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "wq4_common.cuh"
 #include "wq4_model.cuh"
 #include "wq4_ptx.cuh"
@@ -153,6 +155,7 @@ struct EpiCtx {
     int ld;
     __half *sk, *sv;   // QKV: f16 cache rows (clip stride ctx*D), row kvrow
     int ctx, kvrow, D;
+    const int *slot;   // QKV: cache slot of batch row m (active-set compaction) or null = m
 };
 __device__ __forceinline__ void epi_apply(const EpiCtx &e, int m, int n, float v)
 {
@@ -161,9 +164,10 @@ __device__ __forceinline__ void epi_apply(const EpiCtx &e, int m, int n, float v
     else if (e.kind == EPI_GELU) e.dst[(size_t)m * e.ld + n] = wq4_gelu_tanh(v);
     else {
         const int D = e.D;
+        const int cm = e.slot ? __ldg(e.slot + m) : m;
         if (n < D) e.dst[(size_t)m * e.ld + n] = v;
-        else if (n < 2 * D) e.sk[((size_t)m * e.ctx + e.kvrow) * D + (n - D)] = __ushort_as_half(f32_to_f16_sat_d(v));
-        else e.sv[((size_t)m * e.ctx + e.kvrow) * D + (n - 2 * D)] = __ushort_as_half(f32_to_f16_sat_d(v));
+        else if (n < 2 * D) e.sk[((size_t)cm * e.ctx + e.kvrow) * D + (n - D)] = __ushort_as_half(f32_to_f16_sat_d(v));
+        else e.sv[((size_t)cm * e.ctx + e.kvrow) * D + (n - 2 * D)] = __ushort_as_half(f32_to_f16_sat_d(v));
     }
 }
 
@@ -485,7 +489,8 @@ __device__ __forceinline__ AttnPlan attn_plan(int units, int kv, int grid)
 
 template <bool kFreshKV>
 __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc, const __half *vc, long long ldkv,
-                                        long long bstride, long long hstride, int kv_len, int B, int H, AttnPlan pl, float *part, float *sm)
+                                        long long bstride, long long hstride, int kv_len, int B, int H, AttnPlan pl, float *part, float *sm,
+                                        const int *slot)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 3, dch = lane & 7;
@@ -509,8 +514,9 @@ __device__ __noinline__ void attn_phase(const float *q, int D, const __half *kc,
             qv[0] = a.x * 0.125f; qv[1] = a.y * 0.125f; qv[2] = a.z * 0.125f; qv[3] = a.w * 0.125f;
             qv[4] = c.x * 0.125f; qv[5] = c.y * 0.125f; qv[6] = c.z * 0.125f; qv[7] = c.w * 0.125f;
         }
-        const __half *kb_ = kc + (size_t)b * bstride + (size_t)h * hstride + dch * 8;
-        const __half *vb_ = vc + (size_t)b * bstride + (size_t)h * hstride + dch * 8;
+        const int cb = slot ? __ldg(slot + b) : b;
+        const __half *kb_ = kc + (size_t)cb * bstride + (size_t)h * hstride + dch * 8;
+        const __half *vb_ = vc + (size_t)cb * bstride + (size_t)h * hstride + dch * 8;
         Soft st;
         st.m = -INFINITY; st.l = 0.0f;
 #pragma unroll
@@ -625,12 +631,16 @@ __global__ void __launch_bounds__(kDaW * 32, kDaW == 8 ? 1 : 4)
 dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *__restrict__ kc, const __half *__restrict__ vc,
                            long long ldkv, long long bstride, long long hstride, float *__restrict__ out, __half *__restrict__ out16, int ldo, int kv_len,
                            int H, int nsplit, int append_off,
-                           float *__restrict__ part, int *__restrict__ cnt)
+                           float *__restrict__ part, int *__restrict__ cnt, const int *__restrict__ slot)
 {
     __shared__ float sm[(kDaW) * kPartStride];
     __shared__ int s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int u = blockIdx.x, sp = blockIdx.y, h = u % H, b = u / H;
+    // Active-set compaction (whisper.rs:105-108 per clip): query / output rows are dense (row b), the K/V caches stay where
+    // the clip's slot put them.  The slot table is written by the bookkeeping kernel of an EARLIER step, long before this
+    // kernel's predecessor, so it may be read before the programmatic-launch wait.
+    const int cb = slot ? __ldg(slot + b) : b;
     const int per = (kv_len + nsplit - 1) / nsplit;
     const int k0 = sp * per, k1 = min(kv_len, k0 + per);
     ptx::grid_dep_launch();     // PDL: the following projection may be scheduled and prefetch its weights
@@ -653,7 +663,7 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
             pk.y = (uint32_t)f32_to_f16_sat_d(a.z) | ((uint32_t)f32_to_f16_sat_d(a.w) << 16);
             pk.z = (uint32_t)f32_to_f16_sat_d(d.x) | ((uint32_t)f32_to_f16_sat_d(d.y) << 16);
             pk.w = (uint32_t)f32_to_f16_sat_d(d.z) | ((uint32_t)f32_to_f16_sat_d(d.w) << 16);
-            __half *dst = const_cast<__half *>(isv ? vc : kc) + (size_t)b * bstride + (size_t)h * hstride + (size_t)(kv_len - 1) * ldkv + c * 8;
+            __half *dst = const_cast<__half *>(isv ? vc : kc) + (size_t)cb * bstride + (size_t)h * hstride + (size_t)(kv_len - 1) * ldkv + c * 8;
             *reinterpret_cast<uint4 *>(dst) = pk;
         }
         __syncthreads();
@@ -670,8 +680,8 @@ dec_attention_split_kernel(const float *__restrict__ q, int ldq, const __half *_
     constexpr uint32_t kHalf = 32 * 128, kStage = 2 * kHalf, kWarpRing = kDaStages * kStage;
     const uint32_t ring = ptx::smem_u32(da_ring) + (uint32_t)warp * kWarpRing;
     const uint8_t *ring_p = da_ring + (size_t)warp * kWarpRing;
-    const __half *kb_ = kc + (size_t)b * bstride + (size_t)h * hstride;
-    const __half *vb_ = vc + (size_t)b * bstride + (size_t)h * hstride;
+    const __half *kb_ = kc + (size_t)cb * bstride + (size_t)h * hstride;
+    const __half *vb_ = vc + (size_t)cb * bstride + (size_t)h * hstride;
     const int nblocks = (k1 - k0 + 31) >> 5;                                   // 32-key blocks of this CTA's range
     const int n_it = nblocks > warp ? (nblocks - warp + kDaW - 1) / (kDaW) : 0;   // blocks warp, warp+8, ...
     // chunk id = i*32 + lane of a 32-key block: key kl = 4i + (lane >> 3), 16-byte chunk c = lane & 7 (8 lanes = one 128-byte
@@ -994,39 +1004,39 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
         // P1: LN1 -> fused q|k|v projection; q -> a.q, k/v -> f16 cache row kv_len-1 (decoder.rs:84-92, attention.rs:99-113)
         prefetch_weight(L.out, nullptr, nullptr, D);
         ln_rows<R>(a.x, L.ln1w, L.ln1b, xs, red, D);
-        gemv_phase<R>(L.qkv, xs, red, B, EpiCtx{EPI_QKV, gq, D, sk, sv, ctx, kv_len - 1, D});
+        gemv_phase<R>(L.qkv, xs, red, B, EpiCtx{EPI_QKV, gq, D, sk, sv, ctx, kv_len - 1, D, a.slot});
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P2: self-attention over the cache (attention.rs:115-119)
-        attn_phase<true>(a.q, D, sk, sv, D, (long long)a.ctx * D, 64, kv_len, B, H, per_self, a.part, red);
+        attn_phase<true>(a.q, D, sk, sv, D, (long long)a.ctx * D, 64, kv_len, B, H, per_self, a.part, red, a.slot);
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P3: out projection + residual (decoder.rs:91-92)
         prefetch_weight(L.cq, L.ln2w, L.ln2b, D);
         attn_combine<R>(a.part, D, H, kv_len, per_self, B, xs, red);
-        gemv_phase<R>(L.out, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D});
+        gemv_phase<R>(L.out, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D, nullptr});
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P4: LN2 -> cross-attention query (decoder.rs:95-99, attention.rs:214-217)
         prefetch_weight(L.cout, nullptr, nullptr, D);
         ln_rows<R>(a.x, L.ln2w, L.ln2b, xs, red, D);
-        gemv_phase<R>(L.cq, xs, red, B, EpiCtx{EPI_STORE, gq, D, nullptr, nullptr, 0, 0, D});
+        gemv_phase<R>(L.cq, xs, red, B, EpiCtx{EPI_STORE, gq, D, nullptr, nullptr, 0, 0, D, nullptr});
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P5: cross-attention over the cached encoder K/V (attention.rs:219-233)
-        attn_phase<false>(a.q, D, ck, ck + 64, 128, (long long)a.T_enc * 2 * D, (long long)a.T_enc * 128, a.T_enc, B, H, per_cross, a.part, red);
+        attn_phase<false>(a.q, D, ck, ck + 64, 128, (long long)a.T_enc * 2 * D, (long long)a.T_enc * 128, a.T_enc, B, H, per_cross, a.part, red, a.slot);
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P6: cross out projection + residual (decoder.rs:103-104)
         prefetch_weight(L.fc1, L.ln3w, L.ln3b, D);
         attn_combine<R>(a.part, D, H, a.T_enc, per_cross, B, xs, red);
-        gemv_phase<R>(L.cout, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D});
+        gemv_phase<R>(L.cout, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D, nullptr});
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P7: LN3 -> fc1 + tanh-GELU (layers.rs:35-41,55-56)
         prefetch_weight(L.fc2, nullptr, nullptr, D);
         ln_rows<R>(a.x, L.ln3w, L.ln3b, xs, red, D);
-        gemv_phase<R>(L.fc1, xs, red, B, EpiCtx{EPI_GELU, gh, F, nullptr, nullptr, 0, 0, D});
+        gemv_phase<R>(L.fc1, xs, red, B, EpiCtx{EPI_GELU, gh, F, nullptr, nullptr, 0, 0, D, nullptr});
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
 
         // P8: fc2 + residual (layers.rs:57, decoder.rs:108-110)
@@ -1035,7 +1045,7 @@ __global__ void __launch_bounds__(kDT, 1) decode_step_kernel(const DecodeStepArg
         for (int i = tid; i < R * F / 4; i += kDT)
             reinterpret_cast<float4 *>(xs)[i] = __ldcg(reinterpret_cast<const float4 *>(a.h) + i);
         __syncthreads();
-        gemv_phase<R>(L.fc2, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D});
+        gemv_phase<R>(L.fc2, xs, red, B, EpiCtx{EPI_RESID, gx, D, nullptr, nullptr, 0, 0, D, nullptr});
         grid_barrier(a.barrier, bar_target, a.dev_err, a.timeline);
     }
 
@@ -1177,7 +1187,7 @@ int32_t launch_decode(const DecodeStepArgs &a, int device, cudaStream_t st)
     const size_t red_floats = (size_t)kDT * R > (size_t)kMmaRedFloats ? (size_t)kDT * R : (size_t)kMmaRedFloats;
     const size_t smem = ((size_t)R * (a.F > a.D ? a.F : a.D) + red_floats + 1088) * sizeof(float);
     auto kern = decode_step_kernel<R>;
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];
     if (device < 0 || device >= 64 || !attr_done[device]) {
         WQ4_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         if (device >= 0 && device < 64) attr_done[device] = true;
@@ -1242,7 +1252,7 @@ int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, i
 // per clip.  part: >= B*H*nsplit*68 floats, cnt: >= B*H ints (zero; left zero).  nsplit is chosen here.
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
                                  int64_t hstride, float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
-                                 int64_t part_floats, int *cnt, int device, cudaStream_t st, int64_t append_off)
+                                 int64_t part_floats, int *cnt, int device, cudaStream_t st, int64_t append_off, const int *slot)
 {
     const int64_t units = B * H;
     if (units < 1 || kv_len < 1) return WQ4_OK;
@@ -1258,14 +1268,15 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
     int64_t keys_per_cta = (kv_len + ns - 1) / ns;
     bool wide = keys_per_cta > 512 || units * ns <= sms;      // few units: eight warps per unit even on short rows
     {   // tuning overrides: WQ4_DA_CROSS / WQ4_DA_SELF = "<splits>,<0|1 wide>" (kv_len > 512 counts as cross)
-        static int o_ns[2] = {-1, -1}, o_w[2] = {-1, -1};
-        static bool read = false;
-        if (!read) {
+        struct Ov { int ns[2] = {-1, -1}, w[2] = {-1, -1}; };
+        static const Ov ov = [] {              // read once, thread-safely
+            Ov o;
             const char *e0 = getenv("WQ4_DA_SELF"), *e1 = getenv("WQ4_DA_CROSS");
-            if (e0) sscanf(e0, "%d,%d", &o_ns[0], &o_w[0]);
-            if (e1) sscanf(e1, "%d,%d", &o_ns[1], &o_w[1]);
-            read = true;
-        }
+            if (e0) sscanf(e0, "%d,%d", &o.ns[0], &o.w[0]);
+            if (e1) sscanf(e1, "%d,%d", &o.ns[1], &o.w[1]);
+            return o;
+        }();
+        const int *o_ns = ov.ns, *o_w = ov.w;
         const int c = kv_len > 512 ? 1 : 0;
         if (o_ns[c] > 0) {
             ns = o_ns[c];
@@ -1274,7 +1285,7 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
         }
         if (o_w[c] >= 0) wide = o_w[c] != 0;
     }
-    static bool configured[64] = {};
+    static std::atomic<bool> configured[64];
     if (!configured[device & 63]) {
         WQ4_CUDA(cudaFuncSetAttribute(dec_attention_split_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)da_smem(8)));
         WQ4_CUDA(cudaFuncSetAttribute(dec_attention_split_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)da_smem(2)));
@@ -1293,11 +1304,11 @@ int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, co
     if (wide)
         WQ4_CUDA(cudaLaunchKernelEx(&cfg, dec_attention_split_kernel<8>, q, (int)ldq, reinterpret_cast<const __half *>(kc),
                                     reinterpret_cast<const __half *>(vc), (long long)ldkv, (long long)kv_batch_stride, (long long)hstride, out,
-                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, (int)append_off, part, cnt));
+                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, (int)append_off, part, cnt, slot));
     else
         WQ4_CUDA(cudaLaunchKernelEx(&cfg, dec_attention_split_kernel<2>, q, (int)ldq, reinterpret_cast<const __half *>(kc),
                                     reinterpret_cast<const __half *>(vc), (long long)ldkv, (long long)kv_batch_stride, (long long)hstride, out,
-                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, (int)append_off, part, cnt));
+                                    reinterpret_cast<__half *>(out16), (int)ldo, (int)kv_len, (int)H, (int)ns, (int)append_off, part, cnt, slot));
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

@@ -32,6 +32,8 @@
 #include <mutex>
 #include <type_traits>
 
+#include <atomic>
+
 #include "wq4_common.cuh"
 #include "wq4_ptx.cuh"
 
@@ -489,7 +491,7 @@ int32_t launch_tile(const CUtensorMap &tx, const CUtensorMap &ta, const GemmPara
 {
     using L = SmemLayout<TILE_M>;
     auto kern = q4_gemm_kernel<TILE_M, kDenseA, kBF16>;
-    static bool attr_done[16] = {};   // per device
+    static std::atomic<bool> attr_done[16];   // per device
     if (device < 16 && !attr_done[device]) {
         WQ4_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::alloc));
         attr_done[device] = true;

@@ -37,6 +37,8 @@
 
 #include <mutex>
 
+#include <atomic>
+
 #include "wq4_common.cuh"
 #include "wq4_ptx.cuh"
 
@@ -489,7 +491,7 @@ int32_t launch2(const CUtensorMap &tx, const Gemm2Params &p, int device, cudaStr
 {
     using L = Cfg2<TILE_M>;
     auto kern = q4_gemm2_kernel<TILE_M, kBF16>;
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];
     if (device < 0 || device >= 64 || !attr_done[device]) {
         WQ4_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::alloc));
         if (device >= 0 && device < 64) attr_done[device] = true;

@@ -48,15 +48,16 @@ __device__ __forceinline__ int float_key(float f)
 __device__ __forceinline__ float key_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
 
 __global__ void __launch_bounds__(kMelThreads)
-logmel_frames_kernel(const float *__restrict__ pcm, long long n_samples, const float *__restrict__ fb,
-                     const float *__restrict__ hann, const float2 *__restrict__ tw_g, int n_mels, float *__restrict__ mel,
-                     int *__restrict__ maxkey)
+logmel_frames_kernel(const float *__restrict__ pcm, long long stride, long long n_samples_all, const long long *__restrict__ lens,
+                     const float *__restrict__ fb, const float *__restrict__ hann, const float2 *__restrict__ tw_g, int n_mels,
+                     float *__restrict__ mel, int *__restrict__ maxkey)
 {
     __shared__ float xw[kFramesPerCta][kNfft];
     __shared__ float2 tw[kNfft];
     __shared__ float pw[kFramesPerCta][kBins + 3];
     const int tid = threadIdx.x, b = blockIdx.y, frame0 = blockIdx.x * kFramesPerCta;
-    const float *clip = pcm + (size_t)b * n_samples;
+    const float *clip = pcm + (size_t)b * stride;
+    const long long n_samples = lens ? min(lens[b], stride) : n_samples_all;     // ragged batch: clip b holds lens[b] samples
     for (int i = tid; i < kNfft; i += kMelThreads) tw[i] = tw_g[i];
     for (int i = tid; i < kFramesPerCta * kNfft; i += kMelThreads) {
         const int f = i / kNfft, j = i - f * kNfft;
@@ -179,8 +180,25 @@ extern "C" WQ4_API int32_t wq4_logmel_destroy(wq4_logmel *m)
     return WQ4_OK;
 }
 
+static int32_t logmel_run(const wq4_logmel *m, const float *pcm_dev, int64_t batch, int64_t n_samples, const long long *lens_dev,
+                          float *mel_dev, void *stream);
+
 extern "C" WQ4_API int32_t wq4_logmel_forward(const wq4_logmel *m, const float *pcm_dev, int64_t batch, int64_t n_samples,
                                               float *mel_dev, void *stream)
+{
+    return logmel_run(m, pcm_dev, batch, n_samples, nullptr, mel_dev, stream);
+}
+
+// Ragged batch: clip b occupies pcm_dev[b*stride .. b*stride + lens_dev[b]) (lens_dev: device int64 [batch], each <= stride).
+extern "C" WQ4_API int32_t wq4_logmel_forward_ragged(const wq4_logmel *m, const float *pcm_dev, int64_t batch, int64_t stride,
+                                                     const int64_t *lens_dev, float *mel_dev, void *stream)
+{
+    if (!lens_dev) { wq4_set_error("logmel_forward_ragged: lens_dev is null"); return WQ4_ERR_INVALID; }
+    return logmel_run(m, pcm_dev, batch, stride, reinterpret_cast<const long long *>(lens_dev), mel_dev, stream);
+}
+
+static int32_t logmel_run(const wq4_logmel *m, const float *pcm_dev, int64_t batch, int64_t n_samples, const long long *lens_dev,
+                          float *mel_dev, void *stream)
 {
     if (!m || !pcm_dev || !mel_dev || batch < 1 || n_samples < 1) { wq4_set_error("logmel_forward: null pointer or empty input"); return WQ4_ERR_INVALID; }
     if (batch > kMaxMelBatch) { wq4_set_error("logmel_forward: batch %lld > %d", (long long)batch, kMaxMelBatch); return WQ4_ERR_UNSUPPORTED; }
@@ -189,8 +207,8 @@ extern "C" WQ4_API int32_t wq4_logmel_forward(const wq4_logmel *m, const float *
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     WQ4_CUDA(cudaMemsetAsync(m->maxkey, 0x80, (size_t)batch * sizeof(int), st));      // 0x80808080: below every key
     dim3 grid((kFrames + kFramesPerCta - 1) / kFramesPerCta, (unsigned)batch);
-    logmel_frames_kernel<<<grid, kMelThreads, 0, st>>>(pcm_dev, (long long)n_samples, m->fb, m->hann, m->tw, m->n_mels, mel_dev,
-                                                       m->maxkey);
+    logmel_frames_kernel<<<grid, kMelThreads, 0, st>>>(pcm_dev, (long long)n_samples, (long long)n_samples, lens_dev, m->fb, m->hann, m->tw,
+                                                       m->n_mels, mel_dev, m->maxkey);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     const long long per_clip = (long long)m->n_mels * kFrames, total = per_clip * batch;

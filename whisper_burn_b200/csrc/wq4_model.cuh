@@ -13,7 +13,8 @@ int32_t wq4m_layernorm(const float *x, const float *w, const float *b, float *y3
 int32_t wq4m_cross_kv_pack(const void *src16, void *dst16, int64_t B, int64_t T, int64_t H, cudaStream_t st);
 int32_t wq4m_dec_attention_split(const float *q, int64_t ldq, const void *kc, const void *vc, int64_t ldkv, int64_t kv_batch_stride,
                                  int64_t hstride, float *out, void *out16, int64_t ldo, int64_t B, int64_t H, int64_t kv_len, float *part,
-                                 int64_t part_floats, int *cnt, int device, cudaStream_t st, int64_t append_off = 0);
+                                 int64_t part_floats, int *cnt, int device, cudaStream_t st, int64_t append_off = 0, const int *slot = nullptr);
+// slot: device table, row b of q / out reads and appends the caches of clip slot[b] (active-set compaction); null = b.
 // append_off < 0: K/V are static (cross-attention): their first ring stages are requested before the programmatic-launch wait.
 // append_off > 0: q points into a fused q|k|v row and the kernel first stores the new key / value (q + append_off,
 // q + 2*append_off) of every (clip, head) at cache row kv_len - 1 -- the cache append of a decode step without its own launch.
@@ -32,6 +33,11 @@ int32_t wq4m_argmax(const float *logits, int64_t nb, int64_t V, int64_t lo, int6
                     cudaStream_t st);
 int32_t wq4m_kv_append(const float *qkv, int64_t ld_src, void *kc, void *vc, int64_t ldkv, int64_t kv_batch_stride, int64_t B,
                        int64_t D, int64_t q_len, int64_t pos0, cudaStream_t st);
+
+// Greedy-loop bookkeeping on the device (batches <= 1024 clips): see greedy_bookkeep_kernel.
+int32_t wq4m_greedy_init(int *slot, int *n_active, int *count, int64_t B, cudaStream_t st);
+int32_t wq4m_greedy_bookkeep(const int *next, int *tokens_next, int *slot, int *n_active, int *count, const int *budget,
+                             int *tokens_out, int64_t max_tokens, int eot, cudaStream_t st);
 
 // ---- decode-step megakernel (wq4_decode.cu) ------------------------------------------------------------
 // Decode-layout Q4 weight: rows are dealt to the CTAs of the persistent decode kernel in contiguous ranges of
@@ -71,6 +77,7 @@ struct DecodeStepArgs {           // passed BY VALUE: the per-layer table sits i
     float *arg_scratch;           // [grid][B][2]
     unsigned *barrier;            // grid barrier counter (zeroed before every launch)
     int *dev_err;
+    const int *slot;       // [B] device: cache slot of batch row b (active-set compaction) or null = b
     int kv_clips;          // clips the KV caches were laid out for ([layer][kv_clips][ctx|T_enc][D]); >= B
     long long *timeline;   // debug: kDecTimelineSlots x int64 barrier time stamps, normally NULL
 };

@@ -7,6 +7,8 @@
 
 #include <cstdlib>
 
+#include <atomic>
+
 #include "wq4_common.cuh"
 #include "wq4_ptx.cuh"
 #include "wq4_model.cuh"
@@ -600,6 +602,67 @@ __global__ void __launch_bounds__(256) cross_kv_pack_kernel(const uint4 *__restr
     dst[(((b * H + h) * T + t) * 2 + kv) * 8 + c] = src[i];
 }
 
+
+// Greedy-loop bookkeeping of a batch of clips on the device (WhisperModel::transcribe, whisper.rs:104-125, per clip):
+// consumes the arg-max of the rows still active, appends the token to its clip's output (or retires the clip on EOT /
+// when its token budget is used up), COMPACTS the active set -- surviving rows keep their order and move to the front,
+// the retired clips' cache slots fill the tail -- and writes the tokens the next step embeds.  One CTA; the host never
+// has to look at the tokens between steps (it reads *n_active every few steps to shrink its launches).
+// Rows >= *n_active of a launch that still uses an older, larger row count point at retired clips' slots (their caches
+// are dead storage), so whatever they compute is harmless.
+__global__ void __launch_bounds__(1024) greedy_bookkeep_kernel(const int *__restrict__ next, int *__restrict__ tokens_next,
+                                                               int *__restrict__ slot, int *__restrict__ n_active,
+                                                               int *__restrict__ count, const int *__restrict__ budget,
+                                                               int *__restrict__ tokens_out, int max_tokens, int eot)
+{
+    __shared__ int warp_keep[32];
+    __shared__ int s_total;
+    const int r = threadIdx.x, lane = r & 31, warp = r >> 5;
+    const int n = *n_active;
+    int tok = 0, c = 0;
+    bool keep = false;
+    const bool mine = r < n;
+    if (mine) {
+        tok = next[r];
+        c = slot[r];
+        if (tok != eot) {
+            const int k = count[c];
+            if (k < budget[c]) {
+                tokens_out[(size_t)c * max_tokens + k] = tok;
+                count[c] = k + 1;
+                keep = k + 1 < budget[c];
+            }
+        }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_keep[warp] = __popc(bal);
+    __syncthreads();                                   // also: every read of next / slot above is done
+    if (warp == 0) {
+        int v = warp_keep[lane];
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        warp_keep[lane] = incl - v;                    // exclusive prefix over warps
+        if (lane == 31) s_total = incl;
+    }
+    __syncthreads();
+    const int n_new = s_total;
+    if (mine) {
+        const int before = warp_keep[warp] + __popc(bal & ((1u << lane) - 1u));     // kept rows in front of r
+        const int dst = keep ? before : n_new + (r - before);                       // retired rows fill the tail, in order
+        slot[dst] = c;
+        tokens_next[dst] = keep ? tok : 0;
+    }
+    if (r == 0) *n_active = n_new;
+}
+
+__global__ void greedy_init_kernel(int *slot, int *n_active, int *count, int B)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < B) { slot[r] = r; count[r] = 0; }
+    if (r == 0) *n_active = B;
+}
+
 }  // namespace
 
 // ---- host launchers ------------------------------------------------------------------------------
@@ -708,7 +771,7 @@ int32_t wq4m_logits(const float *x, const float *emb, float *logits, int64_t nb,
             logits_kernel<1><<<grid, 256, D * sizeof(float), st>>>(xs, emb, lg, (int)D, (int)V, 1);
         } else {
             size_t smem = 8 * D * sizeof(float);
-            static bool attr = false;
+            static std::atomic<bool> attr{false};
             if (!attr && smem > 48 * 1024) { cudaFuncSetAttribute(logits_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; }
             logits_kernel<8><<<grid, 256, smem, st>>>(xs, emb, lg, (int)D, (int)V, (int)cnt);
         }
@@ -748,6 +811,23 @@ int32_t wq4m_kv_append(const float *qkv, int64_t ld_src, void *kc, void *vc, int
     dim3 grid((unsigned)q_len, (unsigned)B);
     kv_append_kernel<<<grid, 256, 0, st>>>(qkv, (int)ld_src, reinterpret_cast<__half *>(kc), reinterpret_cast<__half *>(vc),
                                            (int)ldkv, (long long)kv_batch_stride, (int)D, (int)q_len, (int)pos0);
+    wq4_count_launch();
+    WQ4_CUDA(cudaGetLastError());
+    return WQ4_OK;
+}
+
+int32_t wq4m_greedy_init(int *slot, int *n_active, int *count, int64_t B, cudaStream_t st)
+{
+    greedy_init_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(slot, n_active, count, (int)B);
+    wq4_count_launch();
+    WQ4_CUDA(cudaGetLastError());
+    return WQ4_OK;
+}
+
+int32_t wq4m_greedy_bookkeep(const int *next, int *tokens_next, int *slot, int *n_active, int *count, const int *budget,
+                             int *tokens_out, int64_t max_tokens, int eot, cudaStream_t st)
+{
+    greedy_bookkeep_kernel<<<1, 1024, 0, st>>>(next, tokens_next, slot, n_active, count, budget, tokens_out, (int)max_tokens, eot);
     wq4_count_launch();
     WQ4_CUDA(cudaGetLastError());
     return WQ4_OK;

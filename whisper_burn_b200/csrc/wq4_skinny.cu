@@ -49,6 +49,7 @@ struct SkinnyParams {
     __half *kc, *vc;
     long long kv_bstride;
     int kv_ld, kv_pos, kvD;
+    const int *kv_slot;        // row m of x belongs to cache slot kv_slot[m] (active-set compaction); null = m
 };
 
 __device__ __forceinline__ uint32_t ldg_nc32(const uint32_t *p)
@@ -271,7 +272,8 @@ __global__ void __launch_bounds__(32 * sk_max_warps(NT)) q4_skinny_kernel(const 
         if (p.y16) p.y16[oi] = __ushort_as_half(f2h_sat(s));
         if (p.kc && nn >= p.kvD) {
             const bool isv = nn >= 2 * p.kvD;
-            __half *dst = (isv ? p.vc : p.kc) + (size_t)m * p.kv_bstride + (size_t)p.kv_pos * p.kv_ld + (nn - (isv ? 2 : 1) * p.kvD);
+            const int clip = p.kv_slot ? __ldg(p.kv_slot + m) : m;
+            __half *dst = (isv ? p.vc : p.kc) + (size_t)clip * p.kv_bstride + (size_t)p.kv_pos * p.kv_ld + (nn - (isv ? 2 : 1) * p.kvD);
             *dst = __ushort_as_half(f2h_sat(s));
         }
     }
@@ -317,6 +319,7 @@ int32_t wq4_launch_skinny(const LinearArgs &a, const SkinnyExtra *ex)
     if (ex && ex->kc) {
         p.kc = reinterpret_cast<__half *>(ex->kc); p.vc = reinterpret_cast<__half *>(ex->vc);
         p.kv_bstride = ex->kv_batch_stride; p.kv_ld = (int)ex->kv_ld; p.kv_pos = (int)ex->kv_pos; p.kvD = (int)ex->kv_d;
+        p.kv_slot = ex->kv_slot;
     }
     const int mode = a.x_f16 ? 0 : (ln ? 2 : 1);
     const unsigned grid = (unsigned)((w->n + kSRows - 1) / kSRows);

@@ -108,7 +108,11 @@ int32_t wq4_tensor_create(const uint8_t *host_blocks, size_t nbytes, int64_t n, 
     *out = nullptr;
     if (!host_blocks && nbytes) { wq4_set_error("wq4_tensor_create: host_blocks is null"); return WQ4_ERR_INVALID; }
     if (n <= 0 || k <= 0) { wq4_set_error("wq4_tensor_create: shape [%lld,%lld] must be positive", (long long)n, (long long)k); return WQ4_ERR_INVALID; }
-    int64_t num_elements = n * k;
+    int64_t num_elements;
+    if (__builtin_mul_overflow(n, k, &num_elements) || num_elements > (int64_t)1 << 56) {
+        wq4_set_error("wq4_tensor_create: shape [%lld,%lld] overflows", (long long)n, (long long)k);
+        return WQ4_ERR_INVALID;
+    }
     if (num_elements % 32 != 0) {  // tensor.rs:38-41
         wq4_set_error("Q4_0 requires element count divisible by 32, got %lld", (long long)num_elements);
         return WQ4_ERR_SHAPE;

@@ -14,6 +14,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <chrono>
 #include <map>
 #include <string>
 #include <vector>
@@ -33,12 +34,21 @@ struct GgufTensor {
     std::vector<uint64_t> dims;   // as stored (reversed w.r.t. row-major shape)
     uint32_t dtype;               // 0 F32, 1 F16, 2 Q4_0 (reader.rs:27-35)
     uint64_t offset;
-    uint64_t num_elements() const { uint64_t n = 1; for (auto d : dims) n *= d; return n; }
-    uint64_t byte_size() const    // reader.rs:38-48
+    // Every size derived from file-controlled values is computed with overflow checks (a crafted file must fail cleanly,
+    // as the reference's reader does on short reads); `bad` marks a tensor whose element or byte count does not fit 64 bits.
+    bool bad = false;
+    uint64_t elems = 0, bytes = 0;
+    void finalize()
     {
-        uint64_t n = num_elements();
-        return dtype == 0 ? n * 4 : dtype == 1 ? n * 2 : n / 32 * 18;
+        uint64_t n = 1;
+        for (auto d : dims) if (__builtin_mul_overflow(n, d, &n)) { bad = true; return; }
+        elems = n;
+        if (dtype == 0) { if (__builtin_mul_overflow(n, (uint64_t)4, &bytes)) bad = true; }
+        else if (dtype == 1) { if (__builtin_mul_overflow(n, (uint64_t)2, &bytes)) bad = true; }
+        else bytes = n / 32 * 18;             // reader.rs:38-48
     }
+    uint64_t num_elements() const { return elems; }
+    uint64_t byte_size() const { return bytes; }
 };
 
 struct Gguf {
@@ -52,7 +62,7 @@ struct Gguf {
 
     bool rd(size_t &pos, void *dst, size_t n)
     {
-        if (pos + n > size) { err = "unexpected end of GGUF data"; return false; }
+        if (pos > size || n > size - pos) { err = "unexpected end of GGUF data"; return false; }
         memcpy(dst, data + pos, n);
         pos += n;
         return true;
@@ -61,20 +71,27 @@ struct Gguf {
     {
         uint64_t n;
         if (!rd(pos, &n, 8)) return false;
-        if (pos + n > size) { err = "unexpected end of GGUF string"; return false; }
+        if (n > size - pos) { err = "unexpected end of GGUF string"; return false; }   // pos <= size after rd()
         s.assign(reinterpret_cast<const char *>(data + pos), (size_t)n);
         pos += (size_t)n;
         return true;
     }
-    bool skip_value(size_t &pos, uint32_t t)   // reader.rs:237-285
+    bool skip_value(size_t &pos, uint32_t t, int depth = 0)   // reader.rs:237-285
     {
         static const int sz[13] = {1, 1, 2, 2, 4, 4, 4, 1, -1, -2, 8, 8, 8};
         if (t > 12) { err = "Unknown GGUF metadata value type"; return false; }
-        if (sz[t] > 0) { if (pos + sz[t] > size) { err = "truncated metadata"; return false; } pos += sz[t]; return true; }
+        if (sz[t] > 0) { if ((size_t)sz[t] > size - pos) { err = "truncated metadata"; return false; } pos += sz[t]; return true; }
         if (t == 8) { std::string s; return rd_str(pos, s); }
         uint32_t et; uint64_t cnt;
         if (!rd(pos, &et, 4) || !rd(pos, &cnt, 8)) return false;
-        for (uint64_t i = 0; i < cnt; i++) if (!skip_value(pos, et)) return false;
+        if (depth >= 16) { err = "GGUF metadata arrays nested too deeply"; return false; }   // bounds the recursion on crafted files
+        if (et <= 12 && sz[et] > 0) {                                                         // fixed-size elements: one checked skip
+            uint64_t nb;
+            if (__builtin_mul_overflow(cnt, (uint64_t)sz[et], &nb) || nb > size - pos) { err = "truncated metadata array"; return false; }
+            pos += (size_t)nb;
+            return true;
+        }
+        for (uint64_t i = 0; i < cnt; i++) if (!skip_value(pos, et, depth + 1)) return false;   // each element consumes >= 4 bytes or fails
         return true;
     }
     bool parse(const uint8_t *d, size_t n)     // reader.rs:105-188
@@ -101,8 +118,11 @@ struct Gguf {
             for (uint32_t j = 0; j < nd; j++) if (!rd(pos, &t.dims[j], 8)) return false;
             if (!rd(pos, &t.dtype, 4) || !rd(pos, &t.offset, 8)) return false;
             if (t.dtype > 2) { err = "Unsupported GGML dtype code"; return false; }
+            t.finalize();
+            if (t.bad) { err = "tensor '" + name + "' size overflows 64 bits"; return false; }
             tensors[name] = t;
         }
+        if (pos > size || size - pos < 31) { data_offset = size; return true; }   // no room for a data section: every tensor_data() fails
         data_offset = (pos + 31) / 32 * 32;    // reader.rs:178-179
         return true;
     }
@@ -113,8 +133,9 @@ struct Gguf {
     }
     const uint8_t *tensor_data(const GgufTensor &t) const
     {
-        uint64_t a = data_offset + t.offset;
-        if (a + t.byte_size() > size) return nullptr;
+        uint64_t a;
+        if (t.bad || __builtin_add_overflow(data_offset, t.offset, &a)) return nullptr;
+        if (a > size || t.byte_size() > size - a) return nullptr;
         return data + a;
     }
 };
@@ -145,10 +166,12 @@ struct wq4_whisper {
     float *dec_pos = nullptr;        // [n_text_ctx, D]
     std::vector<DecLayer> dec;
     LNp ln;
-    std::vector<void *> owned;       // device allocations freed at destroy
+    std::vector<void *> owned;       // device allocations that live as long as the model (weights and what is derived from them)
+    std::vector<void *> ws_owned;    // per-batch workspaces: freed and re-allocated when reserve() grows
     size_t weight_bytes = 0;
     // workspaces (reserved for max_batch)
     int64_t max_batch = 0;
+    int64_t kv_batch = 0;            // clips the KV caches are currently laid out for: [layer][kv_batch][...]; set by cross_kv()
     __half *mel_t16 = nullptr, *h1_16 = nullptr, *xn16 = nullptr, *qkv16 = nullptr, *att16 = nullptr, *ffn16 = nullptr,
            *enc16 = nullptr;
     float *x = nullptr, *enc32 = nullptr;
@@ -159,7 +182,8 @@ struct wq4_whisper {
     float *dx = nullptr, *dxn = nullptr, *dqkv = nullptr, *datt = nullptr, *dq = nullptr, *dh = nullptr, *logits = nullptr;
     __half *dxn16 = nullptr, *datt16 = nullptr, *dh16 = nullptr;   // f16 operands of the decoder GEMMs (rows > 8)
     int *d_tokens = nullptr, *d_next = nullptr, *d_sup_eot = nullptr, *d_sup_none = nullptr;
-    int *h_next = nullptr;           // pinned
+    int *h_next = nullptr;           // pinned [max_batch + 1]: language picks; [max_batch] = active-clip count read-back
+    int *d_slot = nullptr, *d_nactive = nullptr, *d_count = nullptr, *d_budget = nullptr, *d_tokens_out = nullptr;   // greedy-loop bookkeeping
     void *lin_ws = nullptr;
     size_t lin_ws_bytes = 0;
     int64_t max_q = 8;               // rows per batch item in one decoder call (prompt <= 4 tokens)
@@ -186,14 +210,16 @@ namespace {
     } while (0)
 
 template <typename T>
-int32_t dev_alloc(wq4_whisper *m, T **p, size_t count)
+int32_t dev_alloc(wq4_whisper *m, T **p, size_t count, bool workspace = false)
 {
     void *q = nullptr;
     WQ4_CUDA(cudaMalloc(&q, count * sizeof(T) > 0 ? count * sizeof(T) : 16));
-    m->owned.push_back(q);
+    (workspace ? m->ws_owned : m->owned).push_back(q);
     *p = reinterpret_cast<T *>(q);
     return WQ4_OK;
 }
+template <typename T>
+int32_t ws_alloc(wq4_whisper *m, T **p, size_t count) { return dev_alloc(m, p, count, true); }
 
 int32_t upload_f32(wq4_whisper *m, const Gguf &g, const std::string &name, float **out, uint64_t expect_elems,
                    std::vector<float> *host_copy = nullptr)
@@ -339,85 +365,110 @@ int32_t load_model(wq4_whisper *m, const Gguf &g)
     return load_ln(m, g, "decoder.ln", &m->ln, D);                         // loader.rs:369
 }
 
+// Weight-derived decoder buffers, built once (the first reserve): decode-layout copies of the decoder linears for the
+// one-kernel decode step, the f16 logits matrices.
+int32_t prepare_decoder(wq4_whisper *m)
+{
+    if (m->decode_kernel_ready || m->dec.empty()) return WQ4_OK;
+    const int64_t D = m->D;
+    const int n_cta = wq4m_decode_grid(m->device);
+    m->dec_w_host.resize(m->dec.size());
+    auto mk = [&](const Lin &l, DecWeight *out) -> int32_t {
+        void *a1 = nullptr, *a2 = nullptr;
+        CHK(wq4m_decw_create(l.w, l.bias, n_cta, out, &a1, &a2, nullptr));
+        m->owned.push_back(a1); m->owned.push_back(a2);
+        return WQ4_OK;
+    };
+    for (size_t l = 0; l < m->dec.size(); l++) {
+        DecLayer &L = m->dec[l];
+        DecLayerW &W = m->dec_w_host[l];
+        W.ln1w = L.attn_ln.w; W.ln1b = L.attn_ln.b; W.ln2w = L.cross_ln.w; W.ln2b = L.cross_ln.b;
+        W.ln3w = L.mlp_ln.w; W.ln3b = L.mlp_ln.b;
+        CHK(mk(L.qkv, &W.qkv)); CHK(mk(L.out, &W.out)); CHK(mk(L.cq, &W.cq)); CHK(mk(L.cout, &W.cout));
+        CHK(mk(L.fc1, &W.fc1)); CHK(mk(L.fc2, &W.fc2));
+    }
+    m->Vp = (m->V + 31) / 32 * 32;
+    CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
+    CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
+    CHK(dev_alloc(m, &m->att_part, (size_t)n_cta * 4 * 68));   // [cta][kMaxSeg][68]
+    CHK(dev_alloc(m, &m->arg_scratch, (size_t)n_cta * 8 * 2));
+    CHK(dev_alloc(m, &m->grid_bar, 4));
+    WQ4_CUDA(cudaDeviceSynchronize());
+    m->decode_kernel_ready = true;
+    return WQ4_OK;
+}
+
+// Activation / KV-cache workspaces for up to B clips.  Grows on demand (the reference's WhisperModel has no batch
+// ceiling): a larger request synchronises the device, frees the per-batch buffers and re-allocates them; the contents
+// of the caches are NOT preserved across a growth (a transcription never spans one).  Weight-derived buffers stay.
 int32_t reserve(wq4_whisper *m, int64_t B)
 {
     if (B <= m->max_batch) return WQ4_OK;
-    if (m->max_batch != 0) { wq4_set_error("wq4_whisper_reserve: batch can only be reserved once (have %lld, asked %lld)", (long long)m->max_batch, (long long)B); return WQ4_ERR_INVALID; }
     const int64_t D = m->D, F = m->F, T = m->T_enc, Ld = (int64_t)m->dec.size(), ctx = m->cfg.n_text_ctx;
+    if (m->max_batch != 0) {
+        WQ4_CUDA(cudaDeviceSynchronize());
+        for (void *q : m->ws_owned) cudaFree(q);
+        m->ws_owned.clear();
+        if (m->h_next) { cudaFreeHost(m->h_next); m->h_next = nullptr; }
+        m->max_batch = 0;
+        m->kv_batch = 0;
+    }
     m->Cp1 = (m->cfg.n_mels + 7) / 8 * 8;
     m->Tp1 = m->T_mel + 2;
     m->Tp2 = m->T_mel + 2;   // even, as the stride-2 view requires
     const int64_t M = B * T;
-    CHK(dev_alloc(m, &m->mel_t16, (size_t)(B * m->Tp1 + 4) * m->Cp1));
-    CHK(dev_alloc(m, &m->h1_16, (size_t)(B * m->Tp2 + 4) * D));
+    CHK(ws_alloc(m, &m->mel_t16, (size_t)(B * m->Tp1 + 4) * m->Cp1));
+    CHK(ws_alloc(m, &m->h1_16, (size_t)(B * m->Tp2 + 4) * D));
     WQ4_CUDA(cudaMemset(m->h1_16, 0, (size_t)(B * m->Tp2 + 4) * D * 2));   // pad rows stay zero forever
-    CHK(dev_alloc(m, &m->x, (size_t)M * D));
-    CHK(dev_alloc(m, &m->xn16, (size_t)M * D));
-    CHK(dev_alloc(m, &m->qkv16, (size_t)M * 3 * D));
-    CHK(dev_alloc(m, &m->att16, (size_t)M * D));
-    CHK(dev_alloc(m, &m->ffn16, (size_t)M * F));
-    CHK(dev_alloc(m, &m->enc16, (size_t)M * D));
-    CHK(dev_alloc(m, &m->enc32, (size_t)M * D));
-    CHK(dev_alloc(m, &m->cross_kv, (size_t)Ld * M * 2 * D));
-    CHK(dev_alloc(m, &m->self_k, (size_t)Ld * B * ctx * D));
-    CHK(dev_alloc(m, &m->self_v, (size_t)Ld * B * ctx * D));
+    CHK(ws_alloc(m, &m->x, (size_t)M * D));
+    CHK(ws_alloc(m, &m->xn16, (size_t)M * D));
+    CHK(ws_alloc(m, &m->qkv16, (size_t)M * 3 * D));
+    CHK(ws_alloc(m, &m->att16, (size_t)M * D));
+    CHK(ws_alloc(m, &m->ffn16, (size_t)M * F));
+    CHK(ws_alloc(m, &m->enc16, (size_t)M * D));
+    CHK(ws_alloc(m, &m->enc32, (size_t)M * D));
+    CHK(ws_alloc(m, &m->cross_kv, (size_t)Ld * M * 2 * D));
+    CHK(ws_alloc(m, &m->self_k, (size_t)Ld * B * ctx * D));
+    CHK(ws_alloc(m, &m->self_v, (size_t)Ld * B * ctx * D));
     const int64_t R = B * m->max_q;
-    CHK(dev_alloc(m, &m->dx, (size_t)R * D));
-    CHK(dev_alloc(m, &m->dxn, (size_t)R * D));
-    CHK(dev_alloc(m, &m->dqkv, (size_t)R * 3 * D));
-    CHK(dev_alloc(m, &m->datt, (size_t)R * D));
-    CHK(dev_alloc(m, &m->dq, (size_t)R * D));
-    CHK(dev_alloc(m, &m->dh, (size_t)R * F));
-    CHK(dev_alloc(m, &m->dxn16, (size_t)R * D));
-    CHK(dev_alloc(m, &m->datt16, (size_t)R * D));
-    CHK(dev_alloc(m, &m->dh16, (size_t)R * F));
-    CHK(dev_alloc(m, &m->logits, (size_t)B * m->V));
-    CHK(dev_alloc(m, &m->d_tokens, (size_t)R));
-    CHK(dev_alloc(m, &m->d_next, (size_t)B));
-    CHK(dev_alloc(m, &m->d_sup_eot, (size_t)B));
-    CHK(dev_alloc(m, &m->d_sup_none, (size_t)B));
+    CHK(ws_alloc(m, &m->dx, (size_t)R * D));
+    CHK(ws_alloc(m, &m->dxn, (size_t)R * D));
+    CHK(ws_alloc(m, &m->dqkv, (size_t)R * 3 * D));
+    CHK(ws_alloc(m, &m->datt, (size_t)R * D));
+    CHK(ws_alloc(m, &m->dq, (size_t)R * D));
+    CHK(ws_alloc(m, &m->dh, (size_t)R * F));
+    CHK(ws_alloc(m, &m->dxn16, (size_t)R * D));
+    CHK(ws_alloc(m, &m->datt16, (size_t)R * D));
+    CHK(ws_alloc(m, &m->dh16, (size_t)R * F));
+    CHK(ws_alloc(m, &m->logits, (size_t)B * m->V));
+    CHK(ws_alloc(m, &m->d_tokens, (size_t)R));
+    CHK(ws_alloc(m, &m->d_next, (size_t)B));
+    CHK(ws_alloc(m, &m->d_sup_eot, (size_t)B));
+    CHK(ws_alloc(m, &m->d_sup_none, (size_t)B));
     std::vector<int> e((size_t)B, 50257), n((size_t)B, -1);
     WQ4_CUDA(cudaMemcpy(m->d_sup_eot, e.data(), B * 4, cudaMemcpyHostToDevice));
     WQ4_CUDA(cudaMemcpy(m->d_sup_none, n.data(), B * 4, cudaMemcpyHostToDevice));
-    WQ4_CUDA(cudaMallocHost(&m->h_next, (size_t)B * 4));
+    WQ4_CUDA(cudaMallocHost(&m->h_next, (size_t)(B + 1) * 4));
+    CHK(ws_alloc(m, &m->d_slot, (size_t)B));
+    CHK(ws_alloc(m, &m->d_nactive, (size_t)4));
+    CHK(ws_alloc(m, &m->d_count, (size_t)B));
+    CHK(ws_alloc(m, &m->d_budget, (size_t)B));
+    CHK(ws_alloc(m, &m->d_tokens_out, (size_t)B * 224));
     m->lin_ws_bytes = (size_t)R * (size_t)F * 2 + 4096;   // f32 -> f16 copy of the widest decoder activation
-    CHK(dev_alloc(m, reinterpret_cast<uint8_t **>(&m->lin_ws), m->lin_ws_bytes));
-    // decode-step megakernel: decode-layout weights (rows dealt to one CTA per SM), f16 logits matrix, scratch
+    CHK(ws_alloc(m, reinterpret_cast<uint8_t **>(&m->lin_ws), m->lin_ws_bytes));
     if (!m->dec.empty()) {
-        const int n_cta = wq4m_decode_grid(m->device);
-        m->dec_w_host.resize(m->dec.size());
-        auto mk = [&](const Lin &l, DecWeight *out) -> int32_t {
-            void *a1 = nullptr, *a2 = nullptr;
-            CHK(wq4m_decw_create(l.w, l.bias, n_cta, out, &a1, &a2, nullptr));
-            m->owned.push_back(a1); m->owned.push_back(a2);
-            return WQ4_OK;
-        };
-        for (size_t l = 0; l < m->dec.size(); l++) {
-            DecLayer &L = m->dec[l];
-            DecLayerW &W = m->dec_w_host[l];
-            W.ln1w = L.attn_ln.w; W.ln1b = L.attn_ln.b; W.ln2w = L.cross_ln.w; W.ln2b = L.cross_ln.b;
-            W.ln3w = L.mlp_ln.w; W.ln3b = L.mlp_ln.b;
-            CHK(mk(L.qkv, &W.qkv)); CHK(mk(L.out, &W.out)); CHK(mk(L.cq, &W.cq)); CHK(mk(L.cout, &W.cout));
-            CHK(mk(L.fc1, &W.fc1)); CHK(mk(L.fc2, &W.fc2));
-        }
-        m->Vp = (m->V + 31) / 32 * 32;
-        CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
-        CHK(wq4m_logits_matrix(m->tok_emb, m->tok_emb16t, m->V, m->Vp, D, nullptr));
-        if (B > 1) {   // batches beyond the single-kernel step take the per-op path
+        CHK(prepare_decoder(m));
+        if (B > 1 && !m->tok_emb16) {   // batches beyond the single-kernel step: logits as one dense tensor-core GEMM on f16 rows
             m->Vp256 = (m->V + 255) / 256 * 256;
             CHK(dev_alloc(m, &m->tok_emb16, (size_t)m->Vp256 * D));
             WQ4_CUDA(cudaMemset(m->tok_emb16, 0, (size_t)m->Vp256 * D * 2));
             CHK(wq4_launch_cvt_f32_to_16(m->tok_emb, m->tok_emb16, m->V * D, false, nullptr));
         }
-        CHK(dev_alloc(m, &m->att_part, (size_t)n_cta * 4 * 68));   // [cta][kMaxSeg][68]
-        CHK(dev_alloc(m, &m->arg_scratch, (size_t)n_cta * 8 * 2));
         m->da_part_floats = B * (int64_t)m->cfg.n_text_head * 8 * 68;
-        CHK(dev_alloc(m, &m->da_part, (size_t)m->da_part_floats));
-        CHK(dev_alloc(m, &m->da_cnt, (size_t)(B * m->cfg.n_text_head)));
+        CHK(ws_alloc(m, &m->da_part, (size_t)m->da_part_floats));
+        CHK(ws_alloc(m, &m->da_cnt, (size_t)(B * m->cfg.n_text_head)));
         WQ4_CUDA(cudaMemset(m->da_cnt, 0, (size_t)(B * m->cfg.n_text_head) * sizeof(int)));
-        CHK(dev_alloc(m, &m->grid_bar, 4));
         WQ4_CUDA(cudaDeviceSynchronize());
-        m->decode_kernel_ready = true;
     }
     m->max_batch = B;
     return WQ4_OK;
@@ -445,15 +496,14 @@ int32_t lin_sk(const Lin &l, const float *x32, const void *x16, const LNp *ln, f
 // Largest batch whose decode step runs entirely on the skinny linear; WQ4_SKINNY_STEP_ROWS overrides it (tuning runs).
 static int64_t skinny_step_rows()
 {
-    static int64_t v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_SKINNY_STEP_ROWS"); v = e ? atoll(e) : WQ4_SKINNY_DEFAULT_ROWS; if (v > WQ4_SKINNY_MAX_ROWS) v = WQ4_SKINNY_MAX_ROWS; }
+    // function-local statics with an initialiser are initialised once, thread-safely (C++11)
+    static const int64_t v = [] { const char *e = getenv("WQ4_SKINNY_STEP_ROWS"); int64_t r = e ? atoll(e) : WQ4_SKINNY_DEFAULT_ROWS; return r > WQ4_SKINNY_MAX_ROWS ? (int64_t)WQ4_SKINNY_MAX_ROWS : r; }();
     return v;
 }
 static bool use_skinny_step()
 {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_SKINNY"); v = (e && atoi(e) == 0) ? 0 : 1; }   // 0 = tcgen05 GEMM + separate LN / append (A/B runs)
-    return v == 1;
+    static const bool v = [] { const char *e = getenv("WQ4_SKINNY"); return !(e && atoi(e) == 0); }();   // 0 = tcgen05 GEMM + separate LN / append (A/B runs)
+    return v;
 }
 
 // WhisperEncoder::forward (encoder.rs:87-115) for B clips; mel_dev [B, n_mels, 3000] f32.
@@ -498,6 +548,7 @@ int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
 int32_t cross_kv(wq4_whisper *m, int64_t B, cudaStream_t st)
 {
     const int64_t D = m->D, M = B * m->T_enc;
+    m->kv_batch = B;            // the caches of this transcription are [layer][B][..]; later steps may run fewer rows (compaction)
     for (size_t l = 0; l < m->dec.size(); l++)
     {
         // projection into the (now idle) encoder q|k|v buffer, then repacked head-major [B][H][T][128] for the decode steps
@@ -514,9 +565,8 @@ struct ArgReq { int lo, hi; const int *suppress; int *out; };
 
 static bool use_decode_kernel()
 {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_DECODE_IMPL"); v = (e && atoi(e) == 1) ? 0 : 1; }   // 1 = per-op launches (A/B runs)
-    return v == 1;
+    static const bool v = [] { const char *e = getenv("WQ4_DECODE_IMPL"); return !(e && atoi(e) == 1); }();   // 1 = per-op launches (A/B runs)
+    return v;
 }
 
 // One decode step as a single persistent kernel per group of up to 8 clips (wq4_decode.cu).  Larger batches run the
@@ -532,19 +582,17 @@ constexpr int64_t kDecodeGroup = 8;
 // WQ4_DECODE_F16_MIN overrides it (tuning runs together with WQ4_DECODE_GROUP_MAX).
 static int64_t decode_f16_min_rows()
 {
-    static int64_t v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_DECODE_F16_MIN"); v = e ? atoll(e) : 2; if (v < 1) v = 1; }
+    static const int64_t v = [] { const char *e = getenv("WQ4_DECODE_F16_MIN"); int64_t r = e ? atoll(e) : 2; return r < 1 ? (int64_t)1 : r; }();
     return v;
 }
 
 static int64_t decode_grouped_max()
 {
-    static int64_t v = -1;
-    if (v < 0) { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); v = e ? atoll(e) : 1; if (v < 1) v = 1; }
+    static const int64_t v = [] { const char *e = getenv("WQ4_DECODE_GROUP_MAX"); int64_t r = e ? atoll(e) : 1; return r < 1 ? (int64_t)1 : r; }();
     return v;
 }
 
-int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
+int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st, const int *slot)
 {
     if (m->dec.size() > (size_t)kDecMaxLayers) { wq4_set_error("decode step kernel: more than %d decoder layers", kDecMaxLayers); return WQ4_ERR_UNSUPPORTED; }
     const int64_t D = m->D, F = m->F, ctx = m->cfg.n_text_ctx;
@@ -552,36 +600,43 @@ int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv
         const int64_t gb = B - g0 < kDecodeGroup ? B - g0 : kDecodeGroup;
         DecodeStepArgs a = {};
         for (size_t l = 0; l < m->dec.size(); l++) a.layers[l] = m->dec_w_host[l];
-        a.n_layers = (int)m->dec.size(); a.B = (int)gb; a.kv_clips = (int)B; a.D = (int)D; a.F = (int)F;
+        a.n_layers = (int)m->dec.size(); a.B = (int)gb; a.kv_clips = (int)m->kv_batch; a.D = (int)D; a.F = (int)F;
         a.H = m->cfg.n_text_head; a.V = (int)m->V; a.ctx = (int)ctx; a.T_enc = (int)m->T_enc;
         a.tokens = m->d_tokens + g0; a.tok_emb = m->tok_emb; a.tok_emb16t = m->tok_emb16t; a.Vp = (int)m->Vp; a.pos_emb = m->dec_pos;
         a.emb_pos = (int)emb_pos; a.kv_len = (int)kv_pos0;
         a.x = m->dx + g0 * D; a.q = m->dq + g0 * D; a.h = m->dh + g0 * F; a.part = m->att_part;
-        a.self_k = m->self_k + g0 * ctx * D; a.self_v = m->self_v + g0 * ctx * D;
-        a.cross_kv = m->cross_kv + g0 * m->T_enc * 2 * D;
+        // with a slot table the kernel indexes the caches by clip itself; without one a group is a pointer offset
+        const int64_t c0 = slot ? 0 : g0;
+        a.self_k = m->self_k + c0 * ctx * D; a.self_v = m->self_v + c0 * ctx * D;
+        a.cross_kv = m->cross_kv + c0 * m->T_enc * 2 * D;
         a.lnfw = m->ln.w; a.lnfb = m->ln.b; a.logits = m->logits + g0 * m->V;
         a.arg_lo = arg ? arg->lo : 0; a.arg_hi = arg ? arg->hi : 0; a.suppress = (arg && arg->suppress) ? arg->suppress + g0 : nullptr;
         a.next_out = (arg && arg->out) ? arg->out + g0 : nullptr; a.arg_scratch = m->arg_scratch; a.barrier = m->grid_bar;
         a.dev_err = wq4_error_flag_ptr(m->device);
+        a.slot = slot ? slot + g0 : nullptr;
         if (!a.dev_err) return WQ4_ERR_CUDA;
         CHK(wq4m_decode_step(a, m->device, st));
     }
     return WQ4_OK;
 }
 
-int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st)
+// slot (device, or null): cache slot of batch row b, single-query steps only (active-set compaction of the greedy loop)
+int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0, int64_t kv_pos0, const ArgReq *arg, cudaStream_t st,
+                     const int *slot = nullptr)
 {
+    if (slot && q_len != 1) { wq4_set_error("decoder_pass: a slot table needs q_len == 1"); return WQ4_ERR_INVALID; }
+    if (B > m->kv_batch) { wq4_set_error("decoder_pass: batch %lld exceeds the %lld clips the caches hold (encode / cross K/V first)", (long long)B, (long long)m->kv_batch); return WQ4_ERR_INVALID; }
     if (q_len == 1 && B <= decode_grouped_max() && m->decode_kernel_ready && use_decode_kernel() && m->dec.size() <= (size_t)kDecMaxLayers) {
         if (kv_pos0 + 1 > m->cfg.n_text_ctx || emb_pos0 + 1 > m->cfg.n_text_ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
-        return decode_step_fused(m, B, emb_pos0, kv_pos0, arg, st);
+        return decode_step_fused(m, B, emb_pos0, kv_pos0, arg, st, slot);
     }
     const int64_t D = m->D, F = m->F, R = B * q_len, ctx = m->cfg.n_text_ctx, H = m->cfg.n_text_head;
-    const int64_t M = B * m->T_enc;
+    const int64_t KB = m->kv_batch, M = KB * m->T_enc;          // layer strides of the caches
     if (q_len > m->max_q || kv_pos0 + q_len > ctx || emb_pos0 + q_len > ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
     CHK(wq4m_embed(m->d_tokens, m->tok_emb, m->dec_pos, m->dx, B, q_len, D, emb_pos0, st));
     for (size_t l = 0; l < m->dec.size(); l++) {
         DecLayer &L = m->dec[l];
-        __half *sk = m->self_k + l * (size_t)B * ctx * D, *sv = m->self_v + l * (size_t)B * ctx * D;
+        __half *sk = m->self_k + l * (size_t)KB * ctx * D, *sv = m->self_v + l * (size_t)KB * ctx * D;
         const __half *ck = m->cross_kv + l * (size_t)M * 2 * D;
         // Rows > 8 run on the tensor-core GEMM, whose operand is f16: the producers (LayerNorm, split attention, fc1's
         // epilogue) emit it directly; rows <= 8 use the f32 GEMV.  (f16p = single-query step on the GEMM path.)
@@ -598,14 +653,14 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
             // (q|k|v, cross-q, fc1), appends the new K/V rows to the f16 cache from the q|k|v epilogue and adds the
             // residual in place; the split-KV attention emits the f16 operand of the following projection.
             SkinnyExtra none = {}, kv = {};
-            kv.kc = sk; kv.vc = sv; kv.kv_batch_stride = ctx * D; kv.kv_ld = D; kv.kv_pos = kv_pos0; kv.kv_d = D;
+            kv.kc = sk; kv.vc = sv; kv.kv_batch_stride = ctx * D; kv.kv_ld = D; kv.kv_pos = kv_pos0; kv.kv_d = D; kv.kv_slot = slot;
             CHK(lin_sk(L.qkv, m->dx, nullptr, &L.attn_ln, m->dqkv, nullptr, nullptr, R, 0, kv, st));
             CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, m->datt16, D, B, H, kv_pos0 + 1,
-                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st));
+                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st, 0, slot));
             CHK(lin_sk(L.out, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
             CHK(lin_sk(L.cq, m->dx, nullptr, &L.cross_ln, m->dq, nullptr, nullptr, R, 0, none, st));
             CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, m->datt16, D, B, H,
-                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1));
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1, slot));
             CHK(lin_sk(L.cout, nullptr, m->datt16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
             CHK(lin_sk(L.fc1, m->dx, nullptr, &L.mlp_ln, nullptr, m->dh16, nullptr, R, WQ4_EPI_GELU, none, st));
             CHK(lin_sk(L.fc2, nullptr, m->dh16, nullptr, m->dx, nullptr, m->dx, R, 0, none, st));
@@ -616,7 +671,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         CHK(lin_n(L.qkv, m->dqkv, nullptr, 0));
         if (q_len == 1 && m->da_part)           // the attention kernel appends the new K/V row itself
             CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, f16p ? m->datt16 : nullptr, D, B, H, kv_pos0 + 1,
-                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st, D));
+                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st, D, slot));
         else {
             CHK(wq4m_kv_append(m->dqkv, 3 * D, sk, sv, D, ctx * D, B, D, q_len, kv_pos0, st));
             CHK(wq4m_dec_attention(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, D, B, H, q_len, kv_pos0 + q_len,
@@ -628,7 +683,7 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
         CHK(lin_n(L.cq, m->dq, nullptr, 0));
         if (q_len == 1 && m->da_part)
             CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, f16p ? m->datt16 : nullptr, D, B, H,
-                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1));
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1, slot));
         else
             CHK(wq4m_dec_attention(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, D, B, H, q_len, m->T_enc, -1, st));
         CHK(lin_att(L.cout));
@@ -761,6 +816,7 @@ int32_t wq4_whisper_destroy(wq4_whisper *m)
     wq4_conv1d_destroy(m->conv1);
     wq4_conv1d_destroy(m->conv2);
     for (void *p : m->owned) cudaFree(p);
+    for (void *p : m->ws_owned) cudaFree(p);
     if (m->h_next) cudaFreeHost(m->h_next);
     delete m;
     return WQ4_OK;
@@ -796,27 +852,53 @@ int32_t wq4_whisper_encode(wq4_whisper *m, const float *mel_dev, int64_t batch, 
     return WQ4_OK;
 }
 
+// Reads the sticky device error flag (pipeline / grid-barrier timeouts raise it and the kernel carries on with unsynchronised
+// data): called at the synchronisation points of transcribe so that a timeout is an error, never silently wrong tokens.
+static int32_t check_device_flag(wq4_whisper *m, const char *who)
+{
+    int *p = wq4_error_flag_ptr(m->device);
+    if (!p) return WQ4_ERR_CUDA;
+    int v = 0;
+    WQ4_CUDA(cudaMemcpy(&v, p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (v != 0) { wq4_set_error("%s: device error flag %d (a kernel-side wait timed out); results are invalid", who, v); return WQ4_ERR_CUDA; }
+    return WQ4_OK;
+}
+
 // WhisperModel::transcribe (whisper.rs:51-128) for a batch of clips that share the prompt mode.
 //   lang_tokens[b] >= 0 : explicit language -> prompt [SOT, lang, TRANSCRIBE, NO_TIMESTAMPS] (whisper.rs:67-71)
 //   lang_tokens[b] <  0 : auto-detect       -> decode_step(SOT, 0), argmax over the language range, then
 //                         prompt [lang, TRANSCRIBE, NO_TIMESTAMPS] at positions 0..3 with the self-attention
 //                         cache overwritten (whisper.rs:72-88, decoder.rs:149-151,272-275) -- reproduced as is.
 // All clips of one call must use the same mode.  tokens_out: [batch][224] (host), counts_out: [batch] (host).
-int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t batch, const int32_t *lang_tokens,
-                               int32_t *tokens_out, int32_t *counts_out, int32_t *detected_lang_out, wq4_stream stream)
+// max_new_tokens (host, may be NULL): per-clip token budget, clamped to MAX_TOKENS = 224 (whisper.rs:20) -- a batching
+// extension; NULL is the reference's behaviour.
+//
+// The loop is device-driven: the greedy pick, the EOT / budget test (whisper.rs:105-108), the token append and the
+// compaction of the active set all run in one small bookkeeping kernel per step (greedy_bookkeep_kernel), so the host
+// enqueues steps without reading anything back.  Every kSyncEvery steps it reads the number of clips still active and
+// shrinks the row count of the following launches to it: a retired clip stops occupying GEMV rows and stops streaming
+// its 7.7 MB x layers of cross K/V.  Tokens come back in one copy at the end.
+int32_t wq4_whisper_transcribe_ex(wq4_whisper *m, const float *mel_dev, int64_t batch, const int32_t *lang_tokens,
+                                  const int32_t *max_new_tokens, int32_t *tokens_out, int32_t *counts_out,
+                                  int32_t *detected_lang_out, wq4_stream stream)
 {
     if (!m || !mel_dev || !lang_tokens || !tokens_out || !counts_out || batch <= 0) { wq4_set_error("wq4_whisper_transcribe: invalid argument"); return WQ4_ERR_INVALID; }
+    if (batch > 1024) { wq4_set_error("wq4_whisper_transcribe: at most 1024 clips per call (got %lld); split the batch", (long long)batch); return WQ4_ERR_UNSUPPORTED; }
+    if (m->dec.empty()) { wq4_set_error("wq4_whisper_transcribe: the model was loaded without decoder layers"); return WQ4_ERR_INVALID; }
     DeviceGuard g(m->device);
     CHK(reserve(m, batch));
-    if (batch > m->max_batch) { wq4_set_error("wq4_whisper_transcribe: batch exceeds the reserved size"); return WQ4_ERR_INVALID; }
     const int64_t B = batch;
     cudaStream_t st = (cudaStream_t)stream;
     const wq4_whisper_config &c = m->cfg;
     const int SOT = 50258, EOT = 50257, MAX_TOKENS = 224, MIN_TOKENS = 3;   // whisper.rs:15-20,97
+    const int kSyncEvery = 8;
     const int transcribe_tok = 50260 + c.n_lang, no_ts_tok = transcribe_tok + 4;   // config.rs:66-75
     const bool autodetect = lang_tokens[0] < 0;
     for (int64_t b = 0; b < B; b++)
         if ((lang_tokens[b] < 0) != autodetect) { wq4_set_error("wq4_whisper_transcribe: mixed prompt modes in one batch"); return WQ4_ERR_INVALID; }
+    std::vector<int> budget((size_t)B, MAX_TOKENS);
+    if (max_new_tokens)
+        for (int64_t b = 0; b < B; b++) budget[b] = max_new_tokens[b] < 0 ? 0 : (max_new_tokens[b] > MAX_TOKENS ? MAX_TOKENS : max_new_tokens[b]);
 
     CHK(encode(m, mel_dev, B, st));
     CHK(cross_kv(m, B, st));
@@ -850,36 +932,103 @@ int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t bat
     }
     if (detected_lang_out) for (int64_t b = 0; b < B; b++) detected_lang_out[b] = langs[b];
     WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, prompt.data(), prompt.size() * 4, cudaMemcpyHostToDevice, st));
+    WQ4_CUDA(cudaMemcpyAsync(m->d_budget, budget.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
+    CHK(wq4m_greedy_init(m->d_slot, m->d_nactive, m->d_count, B, st));
     ArgReq first_req = {0, (int)m->V, m->d_sup_eot, m->d_next};            // whisper.rs:98-99
     CHK(decoder_pass(m, B, q_len, 0, 0, &first_req, st));                  // forward_prompt: positions restart at 0
     position += q_len;                                                     // whisper.rs:93
     int64_t kv_len = q_len;                                                // cache now holds the prompt only
 
-    std::vector<int> count((size_t)B, 0);
-    std::vector<char> done((size_t)B, 0);
+    int64_t rows = B;                                                      // rows the next launches run (>= clips still active)
+    int *h_nactive = m->h_next + m->max_batch;
     for (int step = 0; step < MAX_TOKENS; step++) {                        // whisper.rs:104-125
-        WQ4_CUDA(cudaMemcpyAsync(m->h_next, m->d_next, B * 4, cudaMemcpyDeviceToHost, st));
-        WQ4_CUDA(cudaStreamSynchronize(st));
-        bool all_done = true;
-        for (int64_t b = 0; b < B; b++) {
-            if (done[b]) continue;
-            int tok = m->h_next[b];
-            if (tok == EOT) { done[b] = 1; continue; }
-            tokens_out[(size_t)b * MAX_TOKENS + count[b]++] = tok;
-            all_done = false;
-        }
-        if (all_done) break;
+        // consume the pick of the previous pass: append / retire / compact, and stage the next step's input tokens
+        CHK(wq4m_greedy_bookkeep(m->d_next, m->d_tokens, m->d_slot, m->d_nactive, m->d_count, m->d_budget, m->d_tokens_out,
+                                 MAX_TOKENS, EOT, st));
         if (step == MAX_TOKENS - 1) break;   // the reference computes one more step whose result it never uses
         if (position >= c.n_text_ctx || kv_len >= c.n_text_ctx) break;
-        WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, m->d_next, B * 4, cudaMemcpyDeviceToDevice, st));
+        bool look = step % kSyncEvery == kSyncEvery - 1;
+        if (max_new_tokens)                     // a clip that has just used up its budget retires now: shrink at once
+            for (int64_t b = 0; b < B && !look; b++) look = budget[b] == step + 1 || (step == 0 && budget[b] == 0);
+        if (look) {
+            WQ4_CUDA(cudaMemcpyAsync(h_nactive, m->d_nactive, 4, cudaMemcpyDeviceToHost, st));
+            WQ4_CUDA(cudaStreamSynchronize(st));
+            rows = *h_nactive;
+            if (rows <= 0) break;
+        }
         const int *sup = (step + 1 < MIN_TOKENS) ? m->d_sup_eot : m->d_sup_none;   // whisper.rs:120-122
         ArgReq req = {0, (int)m->V, sup, m->d_next};
-        CHK(decoder_pass(m, B, 1, position, kv_len, &req, st));            // whisper.rs:116
+        CHK(decoder_pass(m, rows, 1, position, kv_len, &req, st, m->d_slot));       // whisper.rs:116
         position += 1;
         kv_len += 1;
     }
-    for (int64_t b = 0; b < B; b++) counts_out[b] = count[b];
+    std::vector<int> toks((size_t)B * MAX_TOKENS), count((size_t)B);
+    WQ4_CUDA(cudaMemcpyAsync(toks.data(), m->d_tokens_out, toks.size() * 4, cudaMemcpyDeviceToHost, st));
+    WQ4_CUDA(cudaMemcpyAsync(count.data(), m->d_count, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
+    WQ4_CUDA(cudaStreamSynchronize(st));
+    CHK(check_device_flag(m, "wq4_whisper_transcribe"));
+    for (int64_t b = 0; b < B; b++) {
+        counts_out[b] = count[b];
+        memcpy(tokens_out + (size_t)b * MAX_TOKENS, toks.data() + (size_t)b * MAX_TOKENS, (size_t)count[b] * 4);
+    }
     return WQ4_OK;
+}
+
+int32_t wq4_whisper_transcribe(wq4_whisper *m, const float *mel_dev, int64_t batch, const int32_t *lang_tokens,
+                               int32_t *tokens_out, int32_t *counts_out, int32_t *detected_lang_out, wq4_stream stream)
+{
+    return wq4_whisper_transcribe_ex(m, mel_dev, batch, lang_tokens, nullptr, tokens_out, counts_out, detected_lang_out, stream);
+}
+
+// transcribe() of src/transcribe.rs:34-107 for a batch of utterances, from samples to text-token ids:
+// pad / truncate every clip to 480 000 samples (:46-52), log-mel [n_mels, 3000] (:55-76), WhisperModel::transcribe (:86),
+// drop ids >= 50257 (:96-100).  Resampling (:38-43) and the tokenizer's decode (:102-105) stay on the host side of the
+// reference (CPU code off the hot path): pcm must be 16 kHz mono f32.
+//   pcm_dev   : device, clip b at pcm_dev + b*pcm_stride, n_samples[b] samples (host array; longer than 30 s is truncated)
+//   language  : [batch] language token per clip (>= 0) or < 0 for auto-detect; one mode per call
+//   text_tokens_out [batch][224] / text_counts_out [batch] (host): ids < 50257 only;  raw_* (may be NULL): everything emitted
+//   elapsed_ms_out (may be NULL): wall time of the model part (encoder + decode loop), as transcribe.rs:84-87 measures it
+int32_t wq4_transcribe(wq4_whisper *m, const wq4_logmel *mel, const float *pcm_dev, int64_t pcm_stride, const int64_t *n_samples,
+                       int64_t batch, const int32_t *language, int32_t *text_tokens_out, int32_t *text_counts_out,
+                       int32_t *raw_tokens_out, int32_t *raw_counts_out, double *elapsed_ms_out, wq4_stream stream)
+{
+    if (!m || !mel || !pcm_dev || !n_samples || !language || !text_tokens_out || !text_counts_out || batch <= 0 || pcm_stride <= 0) {
+        wq4_set_error("wq4_transcribe: invalid argument");
+        return WQ4_ERR_INVALID;
+    }
+    for (int64_t b = 0; b < batch; b++)
+        if (n_samples[b] < 0 || n_samples[b] > pcm_stride) { wq4_set_error("wq4_transcribe: n_samples[%lld] = %lld outside 0..pcm_stride", (long long)b, (long long)n_samples[b]); return WQ4_ERR_INVALID; }
+    // (an empty clip is padded to 30 s of silence like any short one, transcribe.rs:46-48: the "too short" bail of :61-63 cannot trigger)
+    DeviceGuard g(m->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n_mels = m->cfg.n_mels, frames = m->T_mel;
+    float *mel_dev = nullptr;
+    int64_t *lens_dev = nullptr;
+    WQ4_CUDA(cudaMalloc(&mel_dev, (size_t)batch * n_mels * frames * 4));
+    if (cudaMalloc(&lens_dev, (size_t)batch * 8) != cudaSuccess) { cudaFree(mel_dev); return wq4_cuda_fail(cudaGetLastError(), "wq4_transcribe alloc"); }
+    int32_t rc = WQ4_OK;
+    std::vector<int32_t> raw((size_t)batch * 224), cnt((size_t)batch);
+    do {
+        if (cudaMemcpyAsync(lens_dev, n_samples, (size_t)batch * 8, cudaMemcpyHostToDevice, st) != cudaSuccess) { rc = wq4_cuda_fail(cudaGetLastError(), "wq4_transcribe copy"); break; }
+        if ((rc = wq4_logmel_forward_ragged(mel, pcm_dev, batch, pcm_stride, lens_dev, mel_dev, st)) != WQ4_OK) break;
+        if (cudaStreamSynchronize(st) != cudaSuccess) { rc = wq4_cuda_fail(cudaGetLastError(), "wq4_transcribe sync"); break; }
+        const auto t0 = std::chrono::steady_clock::now();
+        if ((rc = wq4_whisper_transcribe_ex(m, mel_dev, batch, language, nullptr, raw.data(), cnt.data(), nullptr, st)) != WQ4_OK) break;
+        if (elapsed_ms_out) *elapsed_ms_out = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        for (int64_t b = 0; b < batch; b++) {
+            int n = 0;
+            for (int i = 0; i < cnt[b]; i++) {
+                const int32_t t = raw[(size_t)b * 224 + i];
+                if (t >= 0 && t < 50257) text_tokens_out[(size_t)b * 224 + n++] = t;     // transcribe.rs:96-100
+            }
+            text_counts_out[b] = n;
+            if (raw_counts_out) raw_counts_out[b] = cnt[b];
+            if (raw_tokens_out) memcpy(raw_tokens_out + (size_t)b * 224, raw.data() + (size_t)b * 224, (size_t)cnt[b] * 4);
+        }
+    } while (0);
+    cudaFree(mel_dev);
+    cudaFree(lens_dev);
+    return rc;
 }
 
 // GGUF reader probes (host only, no device needed): GgufReader::{version, tensor_count, tensor_info,
@@ -920,11 +1069,36 @@ int32_t wq4_whisper_decoder_pass(wq4_whisper *m, const int32_t *tokens_host, int
     if (!m || !tokens_host || batch <= 0 || q_len <= 0) { wq4_set_error("wq4_whisper_decoder_pass: invalid argument"); return WQ4_ERR_INVALID; }
     DeviceGuard g(m->device);
     if (batch > m->max_batch) { wq4_set_error("wq4_whisper_decoder_pass: call wq4_whisper_encode first"); return WQ4_ERR_INVALID; }
+    // validated BEFORE the token upload below: d_tokens holds max_batch * max_q entries
+    if (q_len > m->max_q || emb_pos0 < 0 || kv_pos0 < 0 || emb_pos0 + q_len > m->cfg.n_text_ctx || kv_pos0 + q_len > m->cfg.n_text_ctx) {
+        wq4_set_error("wq4_whisper_decoder_pass: q_len %lld (max %lld) / positions %lld, %lld outside the %d-token context", (long long)q_len,
+                      (long long)m->max_q, (long long)emb_pos0, (long long)kv_pos0, m->cfg.n_text_ctx);
+        return WQ4_ERR_INVALID;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     if (recompute_cross) CHK(cross_kv(m, batch, st));
     WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, tokens_host, (size_t)batch * q_len * 4, cudaMemcpyHostToDevice, st));
     CHK(decoder_pass(m, batch, q_len, emb_pos0, kv_pos0, nullptr, st));
     if (logits_dev) WQ4_CUDA(cudaMemcpyAsync(logits_dev, m->logits, (size_t)batch * m->V * 4, cudaMemcpyDeviceToDevice, st));
+    return WQ4_OK;
+}
+
+// Same for one single-query step over a SUBSET of the clips whose caches the model holds: row r of the pass is clip
+// slots_host[r] (the active-set compaction of the greedy loop, exercised directly at the logits level).
+int32_t wq4_whisper_decoder_pass_slots(wq4_whisper *m, const int32_t *tokens_host, const int32_t *slots_host, int64_t rows,
+                                       int64_t emb_pos, int64_t kv_pos, float *logits_dev, wq4_stream stream)
+{
+    if (!m || !tokens_host || !slots_host || rows <= 0) { wq4_set_error("wq4_whisper_decoder_pass_slots: invalid argument"); return WQ4_ERR_INVALID; }
+    DeviceGuard g(m->device);
+    if (rows > m->kv_batch) { wq4_set_error("wq4_whisper_decoder_pass_slots: %lld rows but the caches hold %lld clips", (long long)rows, (long long)m->kv_batch); return WQ4_ERR_INVALID; }
+    for (int64_t r = 0; r < rows; r++)
+        if (slots_host[r] < 0 || slots_host[r] >= m->kv_batch) { wq4_set_error("wq4_whisper_decoder_pass_slots: slot %d outside 0..%lld", slots_host[r], (long long)m->kv_batch - 1); return WQ4_ERR_INVALID; }
+    if (emb_pos < 0 || kv_pos < 0 || emb_pos >= m->cfg.n_text_ctx || kv_pos >= m->cfg.n_text_ctx) { wq4_set_error("wq4_whisper_decoder_pass_slots: position outside the context"); return WQ4_ERR_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    WQ4_CUDA(cudaMemcpyAsync(m->d_tokens, tokens_host, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
+    WQ4_CUDA(cudaMemcpyAsync(m->d_slot, slots_host, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
+    CHK(decoder_pass(m, rows, 1, emb_pos, kv_pos, nullptr, st, m->d_slot));
+    if (logits_dev) WQ4_CUDA(cudaMemcpyAsync(logits_dev, m->logits, (size_t)rows * m->V * 4, cudaMemcpyDeviceToDevice, st));
     return WQ4_OK;
 }
 

@@ -44,11 +44,13 @@ def _as_device(device) -> torch.device:
     return torch.device("cuda", torch.cuda.current_device() if torch.cuda.is_available() else 0)
 
 
-def _check_f32_cuda(x: torch.Tensor, name: str) -> torch.Tensor:
+def _check_f32_cuda(x: torch.Tensor, name: str, device: torch.device | None = None) -> torch.Tensor:
     if not x.is_cuda:
         raise _lib.Wq4Error(4, f"{name} must live on a CUDA device; there is no CPU fallback")
     if x.dtype != torch.float32:
         raise _lib.Wq4Error(1, f"{name} must be float32, got {x.dtype}")
+    if device is not None and x.device != device:      # the library dereferences the pointer on the weights' device
+        raise _lib.Wq4Error(1, f"{name} lives on {x.device}, the weights on {device}")
     return x.contiguous()  # op.rs:50 into_contiguous
 
 
@@ -109,7 +111,7 @@ class Q4Tensor:
 
 
 def _linear_ex(weights: Q4Tensor, bias, x: torch.Tensor, flags: int, residual=None) -> torch.Tensor:
-    x = _check_f32_cuda(x, "input")
+    x = _check_f32_cuda(x, "input", weights.device)
     if x.dim() != 3:
         raise _lib.Wq4Error(2, "Input must be 3D [B, M, K]")          # op.rs:53
     b, m, k = x.shape
@@ -123,11 +125,11 @@ def _linear_ex(weights: Q4Tensor, bias, x: torch.Tensor, flags: int, residual=No
     ws = workspace(dev, nbytes)
     bp = None
     if bias is not None:
-        bias = _check_f32_cuda(bias, "bias")
+        bias = _check_f32_cuda(bias, "bias", dev)
         bp = C.c_void_p(bias.data_ptr())
     rp = None
     if residual is not None:
-        residual = _check_f32_cuda(residual, "residual")
+        residual = _check_f32_cuda(residual, "residual", dev)
         rp = C.c_void_p(residual.data_ptr())
     _lib.check(L.wq4_linear_forward_ex(weights._h, bp, C.c_void_p(x.data_ptr()), None,
                                        C.c_void_p(out.data_ptr()), None, rp, b * m, flags,

@@ -73,11 +73,14 @@ def _bind(L):
     L.wq4_whisper_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
     L.wq4_whisper_encode.argtypes = [vp, vp, i64, vp, vp]
     L.wq4_whisper_transcribe.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp]
+    L.wq4_whisper_transcribe_ex.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp, vp]
+    L.wq4_transcribe.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, vp, vp, vp, vp, vp]
     L.wq4_whisper_decoder_pass.argtypes = [vp, vp, i64, i64, i64, i64, i32, vp, vp]
     L.wq4_whisper_decode_step_device.argtypes = [vp, i64, i64, i64, vp]
+    L.wq4_whisper_decoder_pass_slots.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
     for fn in ("wq4_whisper_config_preset", "wq4_whisper_load_gguf", "wq4_whisper_load_gguf_memory", "wq4_whisper_destroy",
                "wq4_whisper_reserve", "wq4_whisper_info", "wq4_whisper_encode", "wq4_whisper_transcribe",
-               "wq4_whisper_decoder_pass", "wq4_whisper_decode_step_device"):
+               "wq4_whisper_decoder_pass", "wq4_whisper_decode_step_device", "wq4_whisper_transcribe_ex", "wq4_transcribe", "wq4_whisper_decoder_pass_slots"):
         getattr(L, fn).restype = i32
     L._model_bound = True
 
@@ -97,12 +100,17 @@ class WhisperModel:
     def reserve(self, max_batch: int) -> None:
         _lib.check(_lib.lib().wq4_whisper_reserve(self._h, int(max_batch)))
 
+    def _check_mel(self, mel: torch.Tensor) -> torch.Tensor:
+        mel = _check_f32_cuda(mel, "mel", self.device)
+        c = self.config
+        if mel.dim() != 3 or mel.shape[0] < 1 or mel.shape[1] != c.n_mels or mel.shape[2] != 2 * c.n_audio_ctx:
+            raise _lib.Wq4Error(2, f"mel must be [B, {c.n_mels}, {2 * c.n_audio_ctx}], got {list(mel.shape)}")
+        return mel
+
     def encode(self, mel: torch.Tensor, want_output: bool = True):
         """mel [B, n_mels, 3000] f32 (device) -> [B, 1500, D] f32 (whisper.rs:41-43)."""
-        mel = _check_f32_cuda(mel, "mel")
+        mel = self._check_mel(mel)
         c = self.config
-        if mel.dim() != 3 or mel.shape[1] != c.n_mels or mel.shape[2] != 2 * c.n_audio_ctx:
-            raise _lib.Wq4Error(2, f"mel must be [B, {c.n_mels}, {2 * c.n_audio_ctx}]")
         b = mel.shape[0]
         out = torch.empty((b, c.n_audio_ctx, self.d_model), dtype=torch.float32, device=self.device) if want_output else None
         _lib.check(_lib.lib().wq4_whisper_encode(self._h, C.c_void_p(mel.data_ptr()), b,
@@ -110,18 +118,23 @@ class WhisperModel:
                                                  C.c_void_p(_stream(self.device))))
         return out
 
-    def transcribe(self, mel: torch.Tensor, lang_code: str | None):
+    def transcribe(self, mel: torch.Tensor, lang_code: str | None, max_new_tokens=None):
         """Greedy decoding (whisper.rs:51-128).  mel [B, n_mels, 3000]; one language (or None = auto)
-        for the whole batch.  Returns (list of token-id lists, list of language tokens)."""
-        mel = _check_f32_cuda(mel, "mel")
+        for the whole batch.  max_new_tokens: optional per-clip token budgets (<= 224).
+        Returns (list of token-id lists, list of language tokens)."""
+        mel = self._check_mel(mel)
         b = mel.shape[0]
         langs = np.full(b, -1 if lang_code is None else lang_token(lang_code), dtype=np.int32)
         toks = np.zeros((b, MAX_TOKENS), dtype=np.int32)
         counts = np.zeros(b, dtype=np.int32)
         det = np.zeros(b, dtype=np.int32)
         vp = lambda a: a.ctypes.data_as(C.c_void_p)
-        _lib.check(_lib.lib().wq4_whisper_transcribe(self._h, C.c_void_p(mel.data_ptr()), b, vp(langs), vp(toks),
-                                                     vp(counts), vp(det), C.c_void_p(_stream(self.device))))
+        budget = None
+        if max_new_tokens is not None:
+            budget = np.ascontiguousarray(np.broadcast_to(np.asarray(max_new_tokens, dtype=np.int32), (b,)))
+        _lib.check(_lib.lib().wq4_whisper_transcribe_ex(self._h, C.c_void_p(mel.data_ptr()), b, vp(langs),
+                                                        None if budget is None else vp(budget), vp(toks),
+                                                        vp(counts), vp(det), C.c_void_p(_stream(self.device))))
         return [toks[i, :counts[i]].tolist() for i in range(b)], det.tolist()
 
     def decoder_pass(self, tokens, emb_pos0: int, kv_pos0: int, recompute_cross: bool = False) -> torch.Tensor:
@@ -132,6 +145,17 @@ class WhisperModel:
         _lib.check(_lib.lib().wq4_whisper_decoder_pass(self._h, t.ctypes.data_as(C.c_void_p), b, q, emb_pos0, kv_pos0,
                                                        1 if recompute_cross else 0, C.c_void_p(out.data_ptr()),
                                                        C.c_void_p(_stream(self.device))))
+        return out
+
+    def decoder_pass_slots(self, tokens, slots, emb_pos: int, kv_pos: int) -> torch.Tensor:
+        """Test hook: one single-query step over the clips `slots` (row r = clip slots[r]) -> logits [rows, vocab]."""
+        t = np.ascontiguousarray(np.asarray(tokens, dtype=np.int32).reshape(-1))
+        sl = np.ascontiguousarray(np.asarray(slots, dtype=np.int32).reshape(-1))
+        assert t.size == sl.size
+        out = torch.empty((t.size, self.vocab), dtype=torch.float32, device=self.device)
+        _lib.check(_lib.lib().wq4_whisper_decoder_pass_slots(self._h, t.ctypes.data_as(C.c_void_p), sl.ctypes.data_as(C.c_void_p),
+                                                             t.size, emb_pos, kv_pos, C.c_void_p(out.data_ptr()),
+                                                             C.c_void_p(_stream(self.device))))
         return out
 
     def decode_step_device(self, batch: int, position: int, kv_len: int) -> None:
@@ -167,6 +191,30 @@ class InferenceState:   # src/transcribe.rs:26-31 (tokenizer omitted: parity is 
     model: WhisperModel
     device: torch.device
     n_mels: int
+
+
+def transcribe(state: InferenceState, samples, language: str | None, mel=None):
+    """transcribe() (src/transcribe.rs:34-107) for a batch of utterances through the single C-ABI call wq4_transcribe:
+    samples = list of 1-D f32 arrays / tensors (16 kHz mono) -> (text-token ids per clip [ids >= 50257 dropped],
+    raw ids per clip, elapsed ms of the model part)."""
+    from .audio import MelSpectrogram
+    mel = mel or MelSpectrogram(state.n_mels, state.device)
+    clips = [torch.as_tensor(s, dtype=torch.float32).reshape(-1) for s in samples]
+    b = len(clips)
+    lens = np.array([int(c.numel()) for c in clips], dtype=np.int64)
+    stride = max(1, int(lens.max()))
+    pcm = torch.zeros((b, stride), dtype=torch.float32, device=state.device)
+    for i, c in enumerate(clips):
+        pcm[i, :c.numel()] = c.to(state.device)
+    langs = np.full(b, -1 if language is None else lang_token(language), dtype=np.int32)
+    text = np.zeros((b, MAX_TOKENS), dtype=np.int32)
+    raw = np.zeros((b, MAX_TOKENS), dtype=np.int32)
+    tc, rc = np.zeros(b, dtype=np.int32), np.zeros(b, dtype=np.int32)
+    ms = C.c_double()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    _lib.check(_lib.lib().wq4_transcribe(state.model._h, mel._h, C.c_void_p(pcm.data_ptr()), stride, vp(lens), b, vp(langs),
+                                         vp(text), vp(tc), vp(raw), vp(rc), C.byref(ms), C.c_void_p(_stream(state.device))))
+    return [text[i, :tc[i]].tolist() for i in range(b)], [raw[i, :rc[i]].tolist() for i in range(b)], ms.value
 
 
 def transcribe_mels(state: InferenceState, mel: torch.Tensor, language: str | None):
