@@ -23,8 +23,8 @@ import whisper_burn_b200 as wb
 from oracle import whisper_np as wn
 
 DEV = "cuda:0"
-LOGIT_TOL = 2e-3
-ENC_TOL = 2e-3
+LOGIT_TOL = 1.8e-3      # 2 x 8.8e-4, the worst measured (Medium, batch 2)
+ENC_TOL = 1.5e-3        # 2 x 7.5e-4, the worst measured (Large-V3 test.wav)
 
 
 @pytest.fixture(autouse=True)
