@@ -81,7 +81,7 @@ def model_logit_elem_bytes():
         L.wq4_logits_elem_bytes.restype = C.c_int32
         return int(L.wq4_logits_elem_bytes())
     except AttributeError:
-        return 4
+        return 2          # the step reads the f16 copy of the embedding matrix
 
 
 if __name__ == "__main__":

@@ -88,3 +88,43 @@ int wq4m_decode_grid(int device);
 int32_t wq4m_decode_step(const DecodeStepArgs &a, int device, cudaStream_t st);
 // f32 [V][D] -> f16 chunks [D/8][Vp] (rows >= V zero)
 int32_t wq4m_logits_matrix(const float *emb, void *dst, int64_t V, int64_t Vp, int64_t D, cudaStream_t st);
+
+// ---- decode step, second generation (wq4_decode2.cu): one cluster per attention head, three grid-wide exchanges per layer ----
+struct Dec2Layer {
+    const uint8_t *wA, *wB, *wC;                                  // [n_cta][sA | sB | sC] weight slabs (see wq4_decode2.cu)
+    const float *ln1w, *ln1b, *ln2w, *ln2b, *ln3w, *ln3b;
+    const float *b_qkv, *b_out, *b_cq, *b_cout, *b_fc1, *b_fc2;    // [N] or null
+};
+struct Dec2Args {                                                // passed BY VALUE (kernel-parameter constant bank)
+    Dec2Layer layers[kDecMaxLayers];
+    int n_layers, D, F, H, V, Vp, ctx, T_enc, CS, kbD;
+    int rq, ro, rc, rf, kpc;                                      // rows per CTA of the q|k|v, out/fc2 slices, cross-q and fc1 jobs; cross keys per CTA
+    uint32_t sA, sB, sC;                                          // slab bytes (multiples of 128)
+    uint32_t a_scl1, a_nib2, a_scl2, b_scl1, b_nib2, b_scl2, c_scl1, c_nib2, c_scl2;   // offsets inside the slabs (nib1 at 0)
+    uint32_t off_bufA;                                            // shared-memory offset of the first weight buffer
+    const int *tokens;
+    const float *tok_emb;
+    const uint4 *tok_emb16t;
+    const float *pos_emb;
+    int emb_pos, kv_len;
+    __half *self_k, *self_v;
+    const __half *cross_kv;
+    int kv_clips;
+    const int *slot;                                              // [1] device: cache slot of the clip, or null = 0
+    const float *lnfw, *lnfb;
+    float *logits;
+    int arg_lo, arg_hi;
+    const int *suppress;
+    int *next_out;
+    float *arg_scratch;                                           // [n_cta][2]
+    float *partial;                                               // [2][H][D]
+    unsigned *barrier;                                            // [0] grid counter, [1] arg-max arrivals (zeroed before every launch)
+    int *dev_err;
+    long long *timeline;
+};
+bool wq4m_dec2_supported(int64_t D, int64_t F, int64_t H);
+int32_t wq4m_dec2_plan(int device, int64_t D, int64_t F, int64_t H, int64_t T_enc, int *cluster_size);
+void wq4m_dec2_geometry(Dec2Args &a, int D, int F, int H, int T_enc, int CS);
+int32_t wq4m_dec2_layer_create(const Dec2Args &geo, const wq4_tensor *qkv, const wq4_tensor *out, const wq4_tensor *cq, const wq4_tensor *cout,
+                               const wq4_tensor *fc1, const wq4_tensor *fc2, Dec2Layer *L, cudaStream_t st);
+int32_t wq4m_decode2_step(const Dec2Args &a, int device, cudaStream_t st);

@@ -189,6 +189,10 @@ struct wq4_whisper {
     int64_t max_q = 8;               // rows per batch item in one decoder call (prompt <= 4 tokens)
     // decode-step megakernel state (wq4_decode.cu): decode-layout copies of the decoder linears, f16 logits matrix
     std::vector<DecLayerW> dec_w_host;
+    bool dec1_ready = false;         // first-generation decode layout built (only when the second generation cannot run, or for A/B runs)
+    Dec2Args dec2 = {};              // second-generation decode step (wq4_decode2.cu): geometry + per-layer slabs
+    bool dec2_ready = false;
+    float *dec2_partial = nullptr;   // [2][H][D]
     uint4 *tok_emb16t = nullptr;     // [D/8][Vp] f16 chunks
     __half *tok_emb16 = nullptr;     // [Vp256][D] f16 rows, zero padded: the dense-GEMM logits of batches above one decode group
     int64_t Vp256 = 0;
@@ -367,25 +371,54 @@ int32_t load_model(wq4_whisper *m, const Gguf &g)
 
 // Weight-derived decoder buffers, built once (the first reserve): decode-layout copies of the decoder linears for the
 // one-kernel decode step, the f16 logits matrices.
+static int64_t decode_grouped_max();
+static bool force_decode_v1()
+{
+    static const bool v = [] { const char *e = getenv("WQ4_DECODE_V1"); return e && atoi(e) == 1; }();   // A/B runs: first-generation kernel
+    return v;
+}
+
 int32_t prepare_decoder(wq4_whisper *m)
 {
     if (m->decode_kernel_ready || m->dec.empty()) return WQ4_OK;
     const int64_t D = m->D;
     const int n_cta = wq4m_decode_grid(m->device);
-    m->dec_w_host.resize(m->dec.size());
-    auto mk = [&](const Lin &l, DecWeight *out) -> int32_t {
-        void *a1 = nullptr, *a2 = nullptr;
-        CHK(wq4m_decw_create(l.w, l.bias, n_cta, out, &a1, &a2, nullptr));
-        m->owned.push_back(a1); m->owned.push_back(a2);
-        return WQ4_OK;
-    };
-    for (size_t l = 0; l < m->dec.size(); l++) {
-        DecLayer &L = m->dec[l];
-        DecLayerW &W = m->dec_w_host[l];
-        W.ln1w = L.attn_ln.w; W.ln1b = L.attn_ln.b; W.ln2w = L.cross_ln.w; W.ln2b = L.cross_ln.b;
-        W.ln3w = L.mlp_ln.w; W.ln3b = L.mlp_ln.b;
-        CHK(mk(L.qkv, &W.qkv)); CHK(mk(L.out, &W.out)); CHK(mk(L.cq, &W.cq)); CHK(mk(L.cout, &W.cout));
-        CHK(mk(L.fc1, &W.fc1)); CHK(mk(L.fc2, &W.fc2));
+    // second generation (one cluster per head): whenever the model's shape and the device allow it
+    int cs = 0;
+    if (!force_decode_v1() && m->dec.size() <= (size_t)kDecMaxLayers)
+        CHK(wq4m_dec2_plan(m->device, D, m->F, m->cfg.n_text_head, m->T_enc, &cs));
+    if (cs > 0) {
+        wq4m_dec2_geometry(m->dec2, (int)D, (int)m->F, m->cfg.n_text_head, (int)m->T_enc, cs);
+        for (size_t l = 0; l < m->dec.size(); l++) {
+            DecLayer &L = m->dec[l];
+            Dec2Layer &W = m->dec2.layers[l];
+            CHK(wq4m_dec2_layer_create(m->dec2, L.qkv.w, L.out.w, L.cq.w, L.cout.w, L.fc1.w, L.fc2.w, &W, nullptr));
+            m->owned.push_back(const_cast<uint8_t *>(W.wA)); m->owned.push_back(const_cast<uint8_t *>(W.wB)); m->owned.push_back(const_cast<uint8_t *>(W.wC));
+            W.ln1w = L.attn_ln.w; W.ln1b = L.attn_ln.b; W.ln2w = L.cross_ln.w; W.ln2b = L.cross_ln.b; W.ln3w = L.mlp_ln.w; W.ln3b = L.mlp_ln.b;
+            W.b_qkv = L.qkv.bias; W.b_out = L.out.bias; W.b_cq = L.cq.bias; W.b_cout = L.cout.bias; W.b_fc1 = L.fc1.bias; W.b_fc2 = L.fc2.bias;
+        }
+        m->dec2.n_layers = (int)m->dec.size();
+        CHK(dev_alloc(m, &m->dec2_partial, (size_t)2 * m->cfg.n_text_head * D));
+        m->dec2_ready = true;
+    }
+    // first generation: only when it can be reached (second generation unavailable, or grouped batches asked for by an override)
+    if (!m->dec2_ready || decode_grouped_max() > 1) {
+        m->dec_w_host.resize(m->dec.size());
+        auto mk = [&](const Lin &l, DecWeight *out) -> int32_t {
+            void *a1 = nullptr, *a2 = nullptr;
+            CHK(wq4m_decw_create(l.w, l.bias, n_cta, out, &a1, &a2, nullptr));
+            m->owned.push_back(a1); m->owned.push_back(a2);
+            return WQ4_OK;
+        };
+        for (size_t l = 0; l < m->dec.size(); l++) {
+            DecLayer &L = m->dec[l];
+            DecLayerW &W = m->dec_w_host[l];
+            W.ln1w = L.attn_ln.w; W.ln1b = L.attn_ln.b; W.ln2w = L.cross_ln.w; W.ln2b = L.cross_ln.b;
+            W.ln3w = L.mlp_ln.w; W.ln3b = L.mlp_ln.b;
+            CHK(mk(L.qkv, &W.qkv)); CHK(mk(L.out, &W.out)); CHK(mk(L.cq, &W.cq)); CHK(mk(L.cout, &W.cout));
+            CHK(mk(L.fc1, &W.fc1)); CHK(mk(L.fc2, &W.fc2));
+        }
+        m->dec1_ready = true;
     }
     m->Vp = (m->V + 31) / 32 * 32;
     CHK(dev_alloc(m, &m->tok_emb16t, (size_t)m->Vp * (D / 8)));
@@ -596,6 +629,21 @@ int32_t decode_step_fused(wq4_whisper *m, int64_t B, int64_t emb_pos, int64_t kv
 {
     if (m->dec.size() > (size_t)kDecMaxLayers) { wq4_set_error("decode step kernel: more than %d decoder layers", kDecMaxLayers); return WQ4_ERR_UNSUPPORTED; }
     const int64_t D = m->D, F = m->F, ctx = m->cfg.n_text_ctx;
+    if (B == 1 && m->dec2_ready) {           // second generation: one cluster per head, three grid-wide exchanges per layer
+        Dec2Args a = m->dec2;
+        a.V = (int)m->V; a.Vp = (int)m->Vp; a.ctx = (int)ctx;
+        a.tokens = m->d_tokens; a.tok_emb = m->tok_emb; a.tok_emb16t = m->tok_emb16t; a.pos_emb = m->dec_pos;
+        a.emb_pos = (int)emb_pos; a.kv_len = (int)kv_pos0;
+        a.self_k = m->self_k; a.self_v = m->self_v; a.cross_kv = m->cross_kv; a.kv_clips = (int)m->kv_batch; a.slot = slot;
+        a.lnfw = m->ln.w; a.lnfb = m->ln.b; a.logits = m->logits;
+        a.arg_lo = arg ? arg->lo : 0; a.arg_hi = arg ? arg->hi : 0; a.suppress = (arg && arg->suppress) ? arg->suppress : nullptr;
+        a.next_out = (arg && arg->out) ? arg->out : nullptr; a.arg_scratch = m->arg_scratch; a.partial = m->dec2_partial;
+        a.barrier = m->grid_bar;
+        a.dev_err = wq4_error_flag_ptr(m->device);
+        if (!a.dev_err) return WQ4_ERR_CUDA;
+        return wq4m_decode2_step(a, m->device, st);
+    }
+    if (!m->dec1_ready) { wq4_set_error("decode step kernel: first-generation layout not built"); return WQ4_ERR_UNSUPPORTED; }
     for (int64_t g0 = 0; g0 < B; g0 += kDecodeGroup) {
         const int64_t gb = B - g0 < kDecodeGroup ? B - g0 : kDecodeGroup;
         DecodeStepArgs a = {};
