@@ -74,6 +74,13 @@ extern "C" {
                            b2_dev: *const f32, x_dev: *const f32, y_dev: *mut f32, b: i64, m: i64,
                            workspace_dev: *mut c_void, workspace_bytes: usize, stream: wq4_stream) -> i32;
 
+    // no counterpart in the reference: Q4FFN::forward for <= 8 rows with the hidden block in a
+    // static device array inside the library -- allocates nothing
+    pub fn wq4_ffn_static_limits(max_rows: *mut i64, max_hidden: *mut i64);
+    pub fn wq4_ffn_forward_static(fc1: *const wq4_tensor, b1_dev: *const f32, fc2: *const wq4_tensor,
+                                  b2_dev: *const f32, x_dev: *const f32, y_dev: *mut f32, b: i64, m: i64,
+                                  stream: wq4_stream) -> i32;
+
     pub fn wq4_conv1d_create(host_w: *const f32, host_bias: *const f32, c_out: i64, c_in: i64,
                              ksize: i64, device: i32, stream: wq4_stream,
                              out: *mut *mut wq4_conv1d) -> i32;

@@ -123,6 +123,18 @@ WQ4_API int32_t wq4_ffn_forward(const wq4_tensor *fc1, const float *b1_dev, cons
                                 int64_t m, void *workspace_dev, size_t workspace_bytes,
                                 wq4_stream stream);
 
+/* No counterpart in the reference: added for callers that cannot allocate
+ * device memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
+ * wq4_ffn_forward for b*m <= 8 rows on the CUDA-core GEMV family, but the f32 hidden block lives in a file-scope
+ * __device__ array inside the library (256 KiB per GPU, held until exit) instead of a caller workspace; the call makes
+ * no cudaMalloc / cudaFree and no allocating library call.  Limits (wq4_ffn_static_limits): b*m <= 8 rows and
+ * fc1's N (the hidden width) <= 8192; beyond them it returns WQ4_ERR_WORKSPACE.  All calls on one GPU share the array:
+ * calls that overlap on the GPU (unordered streams) race on it; nothing in it has to start at zero. */
+WQ4_API void wq4_ffn_static_limits(int64_t *max_rows, int64_t *max_hidden);
+WQ4_API int32_t wq4_ffn_forward_static(const wq4_tensor *fc1, const float *b1_dev, const wq4_tensor *fc2,
+                                       const float *b2_dev, const float *x_dev, float *y_dev, int64_t b,
+                                       int64_t m, wq4_stream stream);
+
 /* ---- Conv1D --------------------------------------------------------------------------- */
 /* host_w: [c_out, c_in, ksize] f32 (loader.rs:256-281); host_bias: [c_out] f32. */
 WQ4_API int32_t wq4_conv1d_create(const float *host_w, const float *host_bias, int64_t c_out,

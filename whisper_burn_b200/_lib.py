@@ -74,6 +74,10 @@ def lib() -> C.CDLL:
     L.wq4_ffn_workspace_bytes.argtypes = [vp, vp, i64, i64]
     L.wq4_ffn_workspace_bytes.restype = sz
     L.wq4_ffn_forward.argtypes = [vp, vp, vp, vp, vp, vp, i64, i64, vp, sz, vp]
+    L.wq4_ffn_forward_static.argtypes = [vp, vp, vp, vp, vp, vp, i64, i64, vp]
+    L.wq4_ffn_forward_static.restype = i32
+    L.wq4_ffn_static_limits.argtypes = [C.POINTER(i64), C.POINTER(i64)]
+    L.wq4_ffn_static_limits.restype = None
     L.wq4_conv1d_create.argtypes = [vp, vp, i64, i64, i64, i32, vp, C.POINTER(vp)]
     L.wq4_conv1d_destroy.argtypes = [vp]
     L.wq4_conv1d_workspace_bytes.argtypes = [vp, i64, i64, i64, i64]

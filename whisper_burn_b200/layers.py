@@ -35,6 +35,26 @@ class Q4FFN:
                                      C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(_stream(dev))))
         return out
 
+    def forward_static(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """wq4_ffn_forward_static: <= 8 rows, hidden block in the library's static device array; the caller passes the
+        output buffer and nothing is allocated (no counterpart in the reference; include/wq4.h)."""
+        x = _check_f32_cuda(x, "input")
+        if x.dim() != 3:
+            raise _lib.Wq4Error(2, "Input must be 3D [B, M, K]")
+        b, m, k = x.shape
+        k1 = self.fc1.weights.shape()[1]
+        d = self.fc2.weights.shape()[0]
+        if k != k1:
+            raise _lib.Wq4Error(2, f"K dimension mismatch: input has {k}, weights have {k1}")
+        if out.dtype != torch.float32 or not out.is_contiguous() or tuple(out.shape) != (b, m, d) or out.device != x.device:
+            raise _lib.Wq4Error(1, f"output must be a contiguous f32 [{b}, {m}, {d}] tensor on {x.device}")
+        L = _lib.lib()
+        p = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        _lib.check(L.wq4_ffn_forward_static(self.fc1.weights._h, p(self.fc1.bias), self.fc2.weights._h, p(self.fc2.bias),
+                                            C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), b, m,
+                                            C.c_void_p(_stream(self.fc1.weights.device))))
+        return out
+
 
 class Conv1D:
     """1-D convolution as an implicit-im2col tensor-core GEMM (src/model/layers.rs:61-133).
