@@ -86,6 +86,29 @@ def test_encoder_short_context_reference_written_gguf(golden_dir):
     assert rel_err(got3[0], lg3) < 1e-2
 
 
+def test_cuda_path_against_hf_second_opinion(golden_dir):
+    """The CUDA path held directly to the Hugging Face outputs of scripts/make_golden_hf.py (an implementation independent
+    of oracle/whisper_np.py) on the reference-written GGUF: encoder output and the logits of 12 positions, prompt pass then
+    incremental steps over the f16 KV cache.  Tolerance as for the tiny-model oracle tests (f16 operands / caches)."""
+    fx = np.load(golden_dir / "hf_second_opinion.npz")
+    blob = (golden_dir / "tiny_whisper.gguf").read_bytes()
+    cfg = wn.WhisperConfig(80, 32, 256, 4, 1, 16, 256, 4, 1, 64, 99)
+    model = wb.load_whisper_from_gguf(blob, _cfg_pair(cfg), DEV)
+    got = model.encode(torch.from_numpy(fx["mel"]).to(DEV)).cpu().numpy()
+    e = rel_err(got, fx["enc_out"])
+    print("encoder vs HF rel err", e)
+    assert e < 5e-3
+    toks = fx["tokens"]
+    B = toks.shape[0]
+    lg = model.decoder_pass([[int(t) for t in toks[b, :3]] for b in range(B)], 0, 0, recompute_cross=True).cpu().numpy()
+    worst = max(rel_err(lg[b], fx["logits"][b, 2]) for b in range(B))
+    for p in range(3, toks.shape[1]):
+        lg = model.decoder_pass([[int(toks[b, p])] for b in range(B)], p, p).cpu().numpy()
+        worst = max(worst, max(rel_err(lg[b], fx["logits"][b, p]) for b in range(B)))
+    print("logits vs HF worst rel err", worst)
+    assert worst < 1e-2
+
+
 def test_decoder_logits_teacher_forced(tiny):
     cfg, oracle, model = tiny
     mel = wn.synthetic_mel(1, cfg.n_mels, 3000, seed=12)

@@ -236,7 +236,9 @@ def test_q4_ffn_values(b, m, d, f):
 
 @pytest.mark.parametrize("b,cin,t_in,cout,stride", [(2, 5, 40, 6, 1), (2, 5, 40, 6, 2), (1, 80, 3000, 1024, 1),
                                                     (1, 128, 300, 1280, 1), (2, 256, 300, 256, 2),
-                                                    (1, 1024, 3000, 1024, 2)])
+                                                    (1, 1024, 3000, 1024, 2),
+                                                    # Large-V3 stem at full size (encoder.rs:89,93): (3000, 384, 1280) and (1500, 3840, 1280)
+                                                    (1, 128, 3000, 1280, 1), (1, 1280, 3000, 1280, 2)])
 def test_conv1d_matches_reference_layer(b, cin, t_in, cout, stride):  # layers.rs:77-132
     rng = np.random.default_rng(cin + cout + stride)
     x = rng.standard_normal((b, cin, t_in)).astype(np.float32)

@@ -226,3 +226,25 @@ def test_gguf_reference_written_file(golden_dir):
     assert g.tensors["decoder.blocks.0.cross_attn.key.weight"].dtype == gguf_np.GGML_Q4_0
     assert "decoder.blocks.0.cross_attn.key.bias" not in g.tensors   # loader.rs:208
     assert g.tensors["encoder.conv1.weight"].dims == [3, 80, 256]     # loader.rs:256-258
+
+
+def test_oracle_matches_hf_second_opinion(golden_dir):
+    """The model-level oracle (Conv1D stem, LayerNorm, SDPA, KV cache, logits: rows the reference leaves unpinned) against an
+    INDEPENDENT implementation: Hugging Face Whisper run on the dequantised weights of the GGUF the reference's converter
+    wrote (scripts/make_golden_hf.py -> hf_second_opinion.npz).  Measured 2.4e-7 (encoder) / 8.1e-7 (logits)."""
+    from oracle import whisper_np as wn
+    fx = np.load(golden_dir / "hf_second_opinion.npz")
+    cfg = wn.WhisperConfig(80, 32, 256, 4, 1, 16, 256, 4, 1, 64, 99)
+    o = wn.WhisperOracle((golden_dir / "tiny_whisper.gguf").read_bytes(), cfg)
+    enc = o.encode(fx["mel"])
+    assert np.abs(enc - fx["enc_out"]).max() / np.abs(fx["enc_out"]).max() < 5e-6
+    for b in range(fx["tokens"].shape[0]):
+        toks = [int(t) for t in fx["tokens"][b]]
+        cache = o.new_cache()
+        lg = o.forward_prompt(toks[:3], enc[b:b + 1], cache)           # decoder.rs:251-296: logits of the last prompt position
+        worst = np.abs(lg - fx["logits"][b, 2]).max() / np.abs(fx["logits"][b, 2]).max()
+        for p in range(3, len(toks)):                                  # decoder.rs:306-348: incremental steps over the KV cache
+            lg = o.decode_step(toks[p], p, enc[b:b + 1], cache)
+            worst = max(worst, np.abs(lg - fx["logits"][b, p]).max() / np.abs(fx["logits"][b, p]).max())
+            assert int(lg.argmax()) == int(fx["logits"][b, p].argmax())
+        assert worst < 5e-6, worst
