@@ -136,6 +136,31 @@ int wq4_pick_tile_m2(int64_t rows, int64_t npairs);
 int wq4_gemm_impl();   // 2 (default) or 1 (WQ4_GEMM_IMPL=1: first-generation kernel, kept for A/B runs)
 int wq4_gemm_cluster_size(int64_t np);
 
+// Chain of Q4 GEMMs in one persistent launch with row-block dependencies and the LayerNorm between two of them folded
+// into the consumer's epilogue (wq4_chain.cu).  Problem i reads x16 [rows][K_i] f16 and may depend on problem dep < i
+// (its x16 / residual / stats_in are that problem's outputs); dep = -1: inputs come from the predecessor kernel.
+#define WQ4_CHAIN_MAX 5
+struct ChainGemm {
+    const wq4_tensor *w;
+    const float *bias;        // [N]: bias, or b' = bias + W.beta when cvec is given
+    const float *cvec;        // [N]: W.gamma -> the epilogue applies r*(acc - mu*c) + b' with (mu, r) from stats_in; null = plain
+    const void *x16;          // f16 [rows][K]
+    const float *residual;    // f32 [rows][N] or null (may alias y32)
+    float *y32;               // f32 [rows][N] or null
+    void *y16;                // f16 [rows][N] or null
+    const float *y16_scale;   // [N] multiplied into y16 (gamma of the LayerNorm the consumer folds) or null
+    void *stats_out;          // float2 [N/128][rows]: per 128-column group (sum, sum of squares) of the f32 result rows, or null
+    const void *stats_in;     // float2 [stats_groups][rows] written by problem `dep`
+    int stats_groups;
+    int dep;
+    uint32_t flags;           // WQ4_EPI_GELU
+    int k_stage0, k_stages;   // K range in stages of 128 (k_stages = 0: all of K): the two halves of a split-K weight are two problems
+    int edep_plus1;           // 1 + problem whose row block must be complete before this problem's epilogue reads `residual` (0: none)
+};
+size_t wq4_chain_counter_words(int64_t rows);      // unsigned words of the zero-initialised counter buffer a launch needs
+int wq4_chain_pick_tile_m(int64_t rows);
+int32_t wq4_launch_chain(const ChainGemm *g, int n, int64_t rows, unsigned *counters, int tile_m, cudaStream_t stream);
+
 // Tensor-core GEMM on a dense 16-bit weight (the Conv1D stem).  The activation operand is a
 // strided 3-D view [x_batch][x_rows][x_k] (element strides x_batch_stride / x_row_stride / 1), which
 // is how the im2col matrix of src/model/layers.rs:93-116 is expressed without materialising it:

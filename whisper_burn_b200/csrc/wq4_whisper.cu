@@ -149,7 +149,11 @@ static float f16_bits_to_f32(uint16_t h)
 // ------------------------------------------------------------------------------------------ model
 struct Lin { wq4_tensor *w = nullptr; float *bias = nullptr; };
 struct LNp { float *w = nullptr; float *b = nullptr; };
-struct EncLayer { LNp attn_ln; Lin qkv, out; LNp mlp_ln; Lin fc1, fc2; };
+struct EncLayer {
+    LNp attn_ln; Lin qkv, out; LNp mlp_ln; Lin fc1, fc2;
+    // LayerNorm folded into the consumer GEMM (wq4_chain.cu): c = W.gamma, b' = bias + W.beta for q|k|v (attn_ln) and fc1 (mlp_ln)
+    float *qkv_c = nullptr, *qkv_b2 = nullptr, *fc1_c = nullptr, *fc1_b2 = nullptr;
+};
 struct DecLayer { LNp attn_ln; Lin qkv, out; LNp cross_ln; Lin cq, ckv, cout; LNp mlp_ln; Lin fc1, fc2; };
 
 }  // namespace
@@ -175,6 +179,9 @@ struct wq4_whisper {
     __half *mel_t16 = nullptr, *h1_16 = nullptr, *xn16 = nullptr, *qkv16 = nullptr, *att16 = nullptr, *ffn16 = nullptr,
            *enc16 = nullptr;
     float *x = nullptr, *enc32 = nullptr;
+    float2 *ln_stats_a = nullptr, *ln_stats_b = nullptr;   // [D/128][rows] row partials of the residual stream (wq4_chain.cu)
+    unsigned *chain_ctr = nullptr;                         // row-block arrival counters of the chain launches, zero between launches
+    bool chain_ready = false;
     int64_t Cp1 = 0, Tp1 = 0, Tp2 = 0;
     // decoder state
     __half *cross_kv = nullptr;      // [L][B][H][T_enc][128]: head-major, 64 K | 64 V per key
@@ -212,6 +219,19 @@ namespace {
         int32_t s__ = (st_);              \
         if (s__ != WQ4_OK) return s__;    \
     } while (0)
+
+static bool chain_split_k()
+{
+    // off by default: measured neutral at one Medium clip (2.166 against 2.148 ms per encoder pass): the extra tile epilogues cost what the shorter critical path saves
+    static const bool v = [] { const char *e = getenv("WQ4_CHAIN_SPLITK"); return e && atoi(e) == 1; }();
+    return v;
+}
+// WQ4_CHAIN=0 restores one launch per GEMM and LayerNorm in the encoder blocks (A/B runs)
+static bool chain_enabled()
+{
+    static const bool v = [] { const char *e = getenv("WQ4_CHAIN"); return !(e && atoi(e) == 0); }();
+    return v;
+}
 
 template <typename T>
 int32_t dev_alloc(wq4_whisper *m, T **p, size_t count, bool workspace = false)
@@ -340,6 +360,26 @@ int32_t load_model(wq4_whisper *m, const Gguf &g)
         m->F = n;
     }
     CHK(load_ln(m, g, "encoder.ln_post", &m->ln_post, D));                 // loader.rs:325
+    // LayerNorm fold vectors of the chained encoder block (wq4_chain.cu), f32 GEMV over the Q4 weights
+    m->chain_ready = chain_enabled() && D % 128 == 0 && D <= 2048;
+    if (m->chain_ready) {
+        auto fold = [&](const Lin &l, const LNp &ln, float **c_out, float **b_out) -> int32_t {
+            int64_t n, k;
+            wq4_tensor_shape(l.w, &n, &k);
+            CHK(dev_alloc(m, c_out, (size_t)n));
+            CHK(dev_alloc(m, b_out, (size_t)n));
+            LinearArgs a = {};
+            a.w = l.w; a.bias = nullptr; a.x_f32 = ln.w; a.y_f32 = *c_out; a.rows = 1; a.stream = nullptr;
+            CHK(wq4_launch_gemv(a));
+            a.bias = l.bias; a.x_f32 = ln.b; a.y_f32 = *b_out;
+            return wq4_launch_gemv(a);
+        };
+        for (auto &L : m->enc) {
+            CHK(fold(L.qkv, L.attn_ln, &L.qkv_c, &L.qkv_b2));
+            CHK(fold(L.fc1, L.mlp_ln, &L.fc1_c, &L.fc1_b2));
+        }
+        WQ4_CUDA(cudaDeviceSynchronize());
+    }
     CHK(upload_f32(m, g, "decoder.token_embedding.weight", &m->tok_emb, 0));   // loader.rs:338-339
     {
         const GgufTensor *t = g.find("decoder.token_embedding.weight");
@@ -460,6 +500,13 @@ int32_t reserve(wq4_whisper *m, int64_t B)
     CHK(ws_alloc(m, &m->ffn16, (size_t)M * F));
     CHK(ws_alloc(m, &m->enc16, (size_t)M * D));
     CHK(ws_alloc(m, &m->enc32, (size_t)M * D));
+    if (m->chain_ready) {
+        CHK(ws_alloc(m, &m->ln_stats_a, (size_t)(D / 128) * M));
+        CHK(ws_alloc(m, &m->ln_stats_b, (size_t)(D / 128) * M));
+        const size_t words = wq4_chain_counter_words(M);
+        CHK(ws_alloc(m, &m->chain_ctr, words));
+        WQ4_CUDA(cudaMemset(m->chain_ctr, 0, words * sizeof(unsigned)));
+    }
     CHK(ws_alloc(m, &m->cross_kv, (size_t)Ld * M * 2 * D));
     CHK(ws_alloc(m, &m->self_k, (size_t)Ld * B * ctx * D));
     CHK(ws_alloc(m, &m->self_v, (size_t)Ld * B * ctx * D));
@@ -564,6 +611,53 @@ int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
     b2.ob = T * D; b2.ot = D; b2.on = 1; b2.rb = 0;
     b2.flags = WQ4_EPI_GELU; b2.device = m->device; b2.stream = st;
     CHK(wq4_launch_gemm_dense(b2, wq4_pick_tile_m(T, b2.n_pad / WQ4_PANEL_ROWS * B)));
+    if (m->chain_ready && !m->enc.empty() && M >= 128) {
+        // EncoderBlock::forward (encoder.rs:37-49) as two launches per block: attention, then ONE chained launch of
+        // out-proj(+x) -> [LN2 folded] fc1+GELU -> fc2(+x) -> [next block's LN1 folded] q|k|v (wq4_chain.cu)
+        const int tm = wq4_chain_pick_tile_m(M);
+        const int groups = (int)(D / 128);
+        CHK(wq4m_layernorm(m->x, m->enc[0].attn_ln.w, m->enc[0].attn_ln.b, nullptr, m->xn16, M, D, st));
+        CHK(lin16(m->enc[0].qkv, m->xn16, nullptr, m->qkv16, nullptr, M, 0, st));
+        for (size_t l = 0; l < m->enc.size(); l++) {
+            const EncLayer &L = m->enc[l];
+            const EncLayer *N = l + 1 < m->enc.size() ? &m->enc[l + 1] : nullptr;
+            CHK(wq4m_enc_attention(m->qkv16, m->att16, B, T, D, c.n_audio_head, st));
+            ChainGemm g[WQ4_CHAIN_MAX] = {};
+            int n = 0;
+            g[n].w = L.out.w; g[n].bias = L.out.bias; g[n].x16 = m->att16; g[n].residual = m->x; g[n].y32 = m->x;
+            g[n].y16 = m->xn16; g[n].y16_scale = L.mlp_ln.w; g[n].stats_out = m->ln_stats_a; g[n].dep = -1;
+            const int i_out = n++;
+            g[n].w = L.fc1.w; g[n].bias = L.fc1_b2; g[n].cvec = L.fc1_c; g[n].x16 = m->xn16; g[n].y16 = m->ffn16;
+            g[n].stats_in = m->ln_stats_a; g[n].stats_groups = groups; g[n].dep = i_out; g[n].flags = WQ4_EPI_GELU;
+            const int i_fc1 = n++;
+            // fc2: few column pairs and a long K.  When its tiles cannot fill the CTA pairs it runs as two K halves on
+            // different pairs: the first writes x + bias + partial in place, the second adds its partial to that
+            int64_t fn, fk;
+            wq4_tensor_shape(L.fc2.w, &fn, &fk);
+            const int64_t fc2_tiles = ((fn + 255) / 256) * ((M + tm - 1) / tm), kst = fk / 128;
+            const bool split = chain_split_k() && fc2_tiles * 3 <= (int64_t)wq4_sm_count(m->device) && kst >= 16 && kst % 2 == 0;
+            int i_fc2 = -1;
+            if (split) {
+                g[n].w = L.fc2.w; g[n].bias = L.fc2.bias; g[n].x16 = m->ffn16; g[n].residual = m->x; g[n].y32 = m->x; g[n].dep = i_fc1;
+                g[n].k_stage0 = 0; g[n].k_stages = (int)(kst / 2);
+                const int i_a = n++;
+                g[n].w = L.fc2.w; g[n].bias = nullptr; g[n].x16 = m->ffn16; g[n].residual = m->x; g[n].y32 = m->x; g[n].dep = i_fc1;
+                g[n].k_stage0 = (int)(kst / 2); g[n].k_stages = (int)(kst / 2); g[n].edep_plus1 = i_a + 1;
+                i_fc2 = n++;
+            } else {
+                g[n].w = L.fc2.w; g[n].bias = L.fc2.bias; g[n].x16 = m->ffn16; g[n].residual = m->x; g[n].y32 = m->x; g[n].dep = i_fc1;
+                i_fc2 = n++;
+            }
+            if (N) {
+                g[i_fc2].y16 = m->xn16; g[i_fc2].y16_scale = N->attn_ln.w; g[i_fc2].stats_out = m->ln_stats_b;
+                g[n].w = N->qkv.w; g[n].bias = N->qkv_b2; g[n].cvec = N->qkv_c; g[n].x16 = m->xn16; g[n].y16 = m->qkv16;
+                g[n].stats_in = m->ln_stats_b; g[n].stats_groups = groups; g[n].dep = i_fc2;
+                n++;
+            }
+            CHK(wq4_launch_chain(g, n, M, m->chain_ctr, tm, st));
+        }
+        return wq4m_layernorm(m->x, m->ln_post.w, m->ln_post.b, m->enc32, m->enc16, M, D, st);   // encoder.rs:114
+    }
     for (auto &L : m->enc) {                                               // EncoderBlock::forward, encoder.rs:37-49
         CHK(wq4m_layernorm(m->x, L.attn_ln.w, L.attn_ln.b, nullptr, m->xn16, M, D, st));
         CHK(lin16(L.qkv, m->xn16, nullptr, m->qkv16, nullptr, M, 0, st));
