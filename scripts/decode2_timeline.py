@@ -28,7 +28,10 @@ for rep in range(5):
     L.wq4_debug_decode2_timeline(C.c_void_p(tl.data_ptr()))
     model.decode_step_device(1, kv, kv); torch.cuda.synchronize()
     L.wq4_debug_decode2_timeline(None)
-    t = tl.cpu().numpy(); t = t[t > 0]
+    full = tl.cpu().numpy()
+    sub = full[480:509].astype(np.float64)
+    subs = globals().setdefault("subs", []); subs.append(np.diff(sub) / 1e3)
+    t = full[:480]; t = t[t > 0]
     acc.append(np.diff(t) / 1e3)
 d = np.median(np.stack(acc), axis=0)
 n = len(d) + 1
@@ -42,4 +45,10 @@ per = d[i:i + 31 * len(names)].reshape(31, len(names))
 print("mean layers 1..31 (us):", dict(zip(names, np.round(per.mean(0), 2))))
 print("layer sum (us):", round(float(per.mean(0).sum()), 2))
 print("tail (wait, red+ln+logits, argmax):", np.round(d[i + 31 * len(names):], 2))
+sn = ["A:grid_wait", "A:reduce_x", "A:ln", "A:wait_w", "A:gemv_qkv", "A:cl_sync", "A:attn", "A:attn_xchg", "A:gemv_out", "A:arrive",
+      "B:grid_wait", "B:reduce_x", "B:ln", "B:wait_w", "B:gemv_cq", "B:cl_sync", "B:kv+attn", "B:attn_xchg", "B:gemv_cout", "B:arrive",
+      "C:grid_wait", "C:reduce_x", "C:ln", "C:wait_w", "C:gemv_fc1", "C:cl_sync", "C:gemv_fc2", "C:arrive"]
+sd = np.median(np.stack(subs), axis=0)
+print("layer 2 sub-phases (us, CTA 0 thread 0):")
+for nm, v in zip(sn, sd): print(f"  {nm:14s} {v:6.2f}")
 print("error flag", L.wq4_device_error_flag(0))

@@ -245,37 +245,55 @@ __device__ __forceinline__ void attn_exchange(Soft2 st, const Smem2 &s, int rank
     __syncthreads();
 }
 
-// x <- x + bias + sum over the H partial vectors (this CTA's columns only), pushed to every CTA of the cluster.
-__device__ __forceinline__ void reduce_x(const float *part, const float *bias, const Smem2 &s, int rank, int CS, int D, int H, int ro)
+// The partial D-vectors of a phase (one per cluster) are summed by the memory system: every CTA adds its slice of its
+// cluster's partial into ONE vector of 64-bit fixed-point accumulators (value * 2^28, red.global.add.u64).  Integer
+// addition is associative, so the sum is bit-identical run to run whatever the arrival order, and it is at least as
+// accurate as an f32 sum (resolution 3.7e-9 absolute, range +-3.4e10).  The next phase reads D accumulators (10 KB per
+// CTA out of L2, one round trip) instead of exchanging H partial vectors through distributed shared memory.
+// Three accumulator vectors rotate: phase p adds into p % 3, reads (p - 1) % 3 and clears (p + 1) % 3 (last read in
+// phase p - 1, next written in phase p + 1; both are a grid barrier away).  3 * n_layers phases end on vector 2, which
+// the final stage reads while it clears vector 1; vectors 0 and 1 are clear again when the kernel ends and vector 2 is
+// cleared in phase 1 of the next launch before phase 2 adds into it: no host-side memset per step.
+constexpr float kFixScale = 268435456.0f;            // 2^28
+constexpr float kFixInv = 1.0f / 268435456.0f;
+struct PhasePre { float bias[4]; float4 w, b; };     // per-thread values a phase needs right after the grid barrier, requested before it
+
+__device__ __forceinline__ void phase_prefetch(PhasePre &pp, const float *bias, const float *lnw, const float *lnb, int D)
 {
-    const int c0 = rank * ro, c1 = min(D, c0 + ro);
-    for (int c = c0 + (int)threadIdx.x; c < c1; c += kT) {
-        float v = s.xres[c];
-        if (bias) v += __ldg(bias + c);
-        for (int h0 = 0; h0 < H; h0 += kHC) {
-            float t[kHC];
+    const int tid = threadIdx.x;
 #pragma unroll
-            for (int i = 0; i < kHC; i++) t[i] = (h0 + i < H) ? __ldcg(part + (size_t)(h0 + i) * D + c) : 0.0f;   // all in flight
+    for (int i = 0; i < 4; i++) { const int c = tid + i * kT; pp.bias[i] = (bias && c < D) ? __ldg(bias + c) : 0.0f; }
+    pp.w = make_float4(0.f, 0.f, 0.f, 0.f); pp.b = pp.w;
+    if (tid < (D >> 2)) { pp.w = __ldg(reinterpret_cast<const float4 *>(lnw) + tid); pp.b = __ldg(reinterpret_cast<const float4 *>(lnb) + tid); }
+}
+
+// x <- x + bias + (accumulated partial sums of the previous phase), every CTA for the whole vector (D <= 4 * kT);
+// `clr` = this CTA's share of the vector to clear for the phase after next (null: nothing to clear)
+__device__ __forceinline__ void reduce_x(const long long *acc, const PhasePre &pp, const Smem2 &s, int D, long long *clr, int n_cta)
+{
+    const int tid = threadIdx.x;
+    long long v[4];
 #pragma unroll
-            for (int i = 0; i < kHC; i++) v += t[i];                                                               // fixed order
-        }
-        const uint32_t addr = ptx::smem_u32(s.xres + c);
-        for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(addr, p), v);
-    }
-    ptx::cluster_sync_all();
+    for (int i = 0; i < 4; i++) { const int c = tid + i * kT; v[i] = c < D ? __ldcg(acc + c) : 0ll; }
+    if (clr)
+        for (int c = (int)blockIdx.x * kT + tid; c < D; c += n_cta * kT) clr[c] = 0ll;
+#pragma unroll
+    for (int i = 0; i < 4; i++) { const int c = tid + i * kT; if (c < D) s.xres[c] += pp.bias[i] + __ll2float_rn(v[i]) * kFixInv; }
+    __syncthreads();
+}
+__device__ __forceinline__ void acc_add(long long *acc, float y)
+{
+    atomicAdd(reinterpret_cast<unsigned long long *>(acc), (unsigned long long)__float2ll_rn(y * kFixScale));
 }
 
 // LayerNorm::forward (src/model/layers.rs:23-31) of xres -> xn (padded); D % 4 == 0, D <= 4 * kT
-__device__ __forceinline__ void ln_to_xn(const float *w, const float *b, const Smem2 &s, int D)
+__device__ __forceinline__ void ln_to_xn(const PhasePre &pp, const Smem2 &s, int D)
 {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const bool on = tid < (D >> 2);
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f), ww = v, bb = v;
-    if (on) {
-        v = reinterpret_cast<const float4 *>(s.xres)[tid];
-        ww = __ldg(reinterpret_cast<const float4 *>(w) + tid);
-        bb = __ldg(reinterpret_cast<const float4 *>(b) + tid);
-    }
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 ww = pp.w, bb = pp.b;
+    if (on) v = reinterpret_cast<const float4 *>(s.xres)[tid];
     float sum = warp_sum2((v.x + v.y) + (v.z + v.w));
     if (lane == 0) s.red[warp] = sum;
     __syncthreads();
@@ -300,11 +318,8 @@ __device__ __forceinline__ void ln_to_xn(const float *w, const float *b, const S
 
 __device__ __forceinline__ void grid_arrive(unsigned *counter)
 {
-    __syncthreads();                      // every thread's partial stores are issued
-    if (threadIdx.x == 0) {
-        __threadfence();                  // ... and visible device-wide before the release below
-        red_release_gpu_add(counter, 1u);
-    }
+    __syncthreads();                      // every thread's partial sums are issued
+    if (threadIdx.x == 0) red_release_gpu_add(counter, 1u);    // release: cumulative over the CTA's reductions (bar.sync above)
 }
 __device__ __forceinline__ void grid_wait(const unsigned *counter, unsigned target, int *dev_err)
 {
@@ -352,6 +367,10 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
         if (tl && tl_n < kDecTimelineSlots) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); tl[tl_n++] = t_; } \
     } while (0)
 
+#define STAMP2(id_)                                                                      \
+    do {                                                                                 \
+        if (tl && l == 2) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); tl[480 + (id_)] = t_; } \
+    } while (0)
     if (tid == 0) {
         ptx::mbar_init(barA, 1); ptx::mbar_init(barB, 1); ptx::mbar_init(barC, 1); ptx::mbar_init(barKV, 1);
         ptx::fence_mbar_init();
@@ -398,8 +417,8 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
         const Dec2Layer &L = a.layers[l];
         const uint32_t par = (uint32_t)(l & 1);
         const size_t self_base = ((size_t)l * a.kv_clips + clip) * (size_t)a.ctx * D + (size_t)cl * 64 + dch * 8;
-        float *part_w;                                   // partial buffer this phase writes
-        const float *part_r;                             // ... and the one it reads (written by the previous phase)
+        long long *const accv = reinterpret_cast<long long *>(a.partial);   // [3][D] fixed-point accumulators
+        PhasePre pp;
 
         // ================= phase A: self-attention block (decoder.rs:84-92) =================
         // cached K/V rows of this CTA's key range: requested now, consumed after q is known (they do not depend on this step)
@@ -413,14 +432,19 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
                 vq[p] = ldg_nc16(a.self_v + self_base + (size_t)key * D);
             }
         }
+        STAMP2(0);
+        phase_prefetch(pp, l > 0 ? a.layers[l - 1].b_fc2 : nullptr, L.ln1w, L.ln1b, D);
         if (l > 0) {
             grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
             STAMP();
-            part_r = a.partial + (size_t)((ph - 1) & 1) * H * D;
-            reduce_x(part_r, a.layers[l - 1].b_fc2, s, rank, CS, D, H, a.ro);
+            STAMP2(1);
+            reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
         }
-        ln_to_xn(L.ln1w, L.ln1b, s, D);
+        STAMP2(2);
+        ln_to_xn(pp, s, D);
+        STAMP2(3);
         wait_bar(barA, par);
+        STAMP2(4);
         {   // q_h | k_h | v_h rows of this CTA (attention.rs:99-104): virtual row vr = 64*kind + dim
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufA);
             const __half *scl = reinterpret_cast<const __half *>(s.bufA + a.a_scl1);
@@ -432,8 +456,10 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
                 for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(qb + vr * 4, p), y);
             });
         }
+        STAMP2(5);
         ptx::cluster_sync_all();
         STAMP();
+        STAMP2(6);
         {   // self-attention of head `cl` over keys [sk0, sk1) (attention.rs:106-119); key kv_len-1 is the new row
             if (rank == 0 && tid < 128) {                // append the new K/V row to the f16 cache in place (no realloc)
                 __half *dst = (tid < 64 ? a.self_k : a.self_v) + ((size_t)l * a.kv_clips + clip) * (size_t)a.ctx * D + (size_t)(kv_len - 1) * D + cl * 64 + (tid & 63);
@@ -465,28 +491,35 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
                 }
                 soft_key(st, qv, kk, vv, valid);
             }
+            STAMP2(7);
             attn_exchange(st, s, rank, CS);
         }
         STAMP();
-        part_w = a.partial + (size_t)(ph++ & 1) * H * D;
-        {   // out-projection restricted to the head's 64 input columns -> partial[cl][n] (bias added by the reducer)
+        STAMP2(8);
+        {   // out-projection restricted to the head's 64 input columns, added into the phase's accumulator (bias added by the reader)
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufA + a.a_nib2);
             const __half *scl = reinterpret_cast<const __half *>(s.bufA + a.a_scl2);
             const int n0 = rank * a.ro, rows = max(0, min(D, n0 + a.ro) - n0);
-            float *dst = part_w + (size_t)cl * D + n0;
-            gemv_job<2>(nib, scl, rows, 2, s.atth, [&](int r, float y) { dst[r] = y; });
+            long long *dst = accv + (size_t)(ph++ % 3) * D + n0;
+            gemv_job<2>(nib, scl, rows, 2, s.atth, [&](int r, float y) { acc_add(dst + r, y); });
         }
+        STAMP2(9);
         grid_arrive(a.barrier);
         if (tid == 0 && l + 1 < a.n_layers) { ptx::fence_proxy_async_smem(); issue_A(l + 1); }
         STAMP();
+        STAMP2(10);
 
         // ================= phase B: cross-attention block (decoder.rs:95-104) =================
+        phase_prefetch(pp, L.b_out, L.ln2w, L.ln2b, D);
         grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
         STAMP();
-        part_r = part_w;
-        reduce_x(part_r, L.b_out, s, rank, CS, D, H, a.ro);
-        ln_to_xn(L.ln2w, L.ln2b, s, D);
+        STAMP2(11);
+        reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
+        STAMP2(12);
+        ln_to_xn(pp, s, D);
+        STAMP2(13);
         wait_bar(barB, par);
+        STAMP2(14);
         {   // cross-attention query rows of this CTA (attention.rs:214-217)
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufB);
             const __half *scl = reinterpret_cast<const __half *>(s.bufB + a.b_scl1);
@@ -498,8 +531,10 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
                 for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(qb + vr * 4, p), y);
             });
         }
+        STAMP2(15);
         ptx::cluster_sync_all();
         STAMP();
+        STAMP2(16);
         {   // cross-attention of head `cl` over this CTA's keys, K/V rows resident in shared memory (attention.rs:219-233)
             if (kv_bytes) wait_bar(barKV, par);
             float qv[8];
@@ -520,29 +555,36 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
                 }
                 soft_key(st, qv, kk, vv, valid);
             }
+            STAMP2(17);
             attn_exchange(st, s, rank, CS);        // its first __syncthreads also ends every read of bufKV
             if (tid == 0 && l + 1 < a.n_layers) { ptx::fence_proxy_async_smem(); issue_KV(l + 1); }
         }
         STAMP();
-        part_w = a.partial + (size_t)(ph++ & 1) * H * D;
+        STAMP2(18);
         {
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufB + a.b_nib2);
             const __half *scl = reinterpret_cast<const __half *>(s.bufB + a.b_scl2);
             const int n0 = rank * a.ro, rows = max(0, min(D, n0 + a.ro) - n0);
-            float *dst = part_w + (size_t)cl * D + n0;
-            gemv_job<2>(nib, scl, rows, 2, s.atth, [&](int r, float y) { dst[r] = y; });
+            long long *dst = accv + (size_t)(ph++ % 3) * D + n0;
+            gemv_job<2>(nib, scl, rows, 2, s.atth, [&](int r, float y) { acc_add(dst + r, y); });
         }
+        STAMP2(19);
         grid_arrive(a.barrier);
         if (tid == 0 && l + 1 < a.n_layers) { ptx::fence_proxy_async_smem(); issue_B(l + 1); }
         STAMP();
+        STAMP2(20);
 
         // ================= phase C: feed-forward block (layers.rs:54-58, decoder.rs:107-110) =================
+        phase_prefetch(pp, L.b_cout, L.ln3w, L.ln3b, D);
         grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
         STAMP();
-        part_r = part_w;
-        reduce_x(part_r, L.b_cout, s, rank, CS, D, H, a.ro);
-        ln_to_xn(L.ln3w, L.ln3b, s, D);
+        STAMP2(21);
+        reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
+        STAMP2(22);
+        ln_to_xn(pp, s, D);
+        STAMP2(23);
         wait_bar(barC, par);
+        STAMP2(24);
         {   // fc1 rows of the cluster's 256-wide slice of the hidden layer + tanh-GELU (layers.rs:35-41,55-56)
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufC);
             const __half *scl = reinterpret_cast<const __half *>(s.bufC + a.c_scl1);
@@ -556,27 +598,37 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
                 for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(hb + off, p), y);
             });
         }
+        STAMP2(25);
         ptx::cluster_sync_all();
         STAMP();
-        part_w = a.partial + (size_t)(ph++ & 1) * H * D;
-        {   // fc2 restricted to the slice's 256 input columns -> partial[cl][n]
+        STAMP2(26);
+        {   // fc2 restricted to the slice's 256 input columns, added into the phase's accumulator
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufC + a.c_nib2);
             const __half *scl = reinterpret_cast<const __half *>(s.bufC + a.c_scl2);
             const int n0 = rank * a.ro, rows = max(0, min(D, n0 + a.ro) - n0);
-            float *dst = part_w + (size_t)cl * D + n0;
-            gemv_job<8>(nib, scl, rows, 8, s.hsl, [&](int r, float y) { dst[r] = y; });
+            long long *dst = accv + (size_t)(ph++ % 3) * D + n0;
+            gemv_job<8>(nib, scl, rows, 8, s.hsl, [&](int r, float y) { acc_add(dst + r, y); });
         }
+        STAMP2(27);
         grid_arrive(a.barrier);
         if (tid == 0 && l + 1 < a.n_layers) { ptx::fence_proxy_async_smem(); issue_C(l + 1); }
         STAMP();
+        STAMP2(28);
     }
 
     // ---- final LayerNorm + logits = x . token_embedding^T (decoder.rs:338-343) against the f16 transposed matrix
     // ([D/8][Vp] 16-byte chunks: lane = vocabulary row, coalesced, no cross-lane reduction), greedy pick (whisper.rs:131-138)
-    grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
-    STAMP();
-    reduce_x(a.partial + (size_t)((ph - 1) & 1) * H * D, a.layers[a.n_layers - 1].b_fc2, s, rank, CS, D, H, a.ro);
-    ln_to_xn(a.lnfw, a.lnfb, s, D);
+    {
+        PhasePre pp;
+        phase_prefetch(pp, a.layers[a.n_layers - 1].b_fc2, a.lnfw, a.lnfb, D);
+        grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
+        STAMP();
+        // reads vector 2 and clears vector 1 (read in the last phase); vector 0 was cleared in the last phase, vector 2 is
+        // cleared in phase 1 of the next launch, before phase 2 adds into it
+        long long *const accv = reinterpret_cast<long long *>(a.partial);
+        reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
+        ln_to_xn(pp, s, D);
+    }
     const int V = a.V, Vp = a.Vp, chunks = D >> 3;
     const bool pick = a.arg_hi > a.arg_lo && a.next_out != nullptr;
     float best = -INFINITY;
@@ -646,6 +698,7 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
     }
     STAMP();
 #undef STAMP
+#undef STAMP2
 }
 
 // ---- decode layout builder: panel layout -> per-CTA slabs -----------------------------------------------------------

@@ -199,7 +199,7 @@ struct wq4_whisper {
     bool dec1_ready = false;         // first-generation decode layout built (only when the second generation cannot run, or for A/B runs)
     Dec2Args dec2 = {};              // second-generation decode step (wq4_decode2.cu): geometry + per-layer slabs
     bool dec2_ready = false;
-    float *dec2_partial = nullptr;   // [2][H][D]
+    float *dec2_partial = nullptr;   // [3][D] int64 fixed-point accumulators
     uint4 *tok_emb16t = nullptr;     // [D/8][Vp] f16 chunks
     __half *tok_emb16 = nullptr;     // [Vp256][D] f16 rows, zero padded: the dense-GEMM logits of batches above one decode group
     int64_t Vp256 = 0;
@@ -438,7 +438,9 @@ int32_t prepare_decoder(wq4_whisper *m)
             W.b_qkv = L.qkv.bias; W.b_out = L.out.bias; W.b_cq = L.cq.bias; W.b_cout = L.cout.bias; W.b_fc1 = L.fc1.bias; W.b_fc2 = L.fc2.bias;
         }
         m->dec2.n_layers = (int)m->dec.size();
-        CHK(dev_alloc(m, &m->dec2_partial, (size_t)2 * m->cfg.n_text_head * D));
+        // [3][D] 64-bit fixed-point accumulators of the phase exchanges (wq4_decode2.cu), zero between launches
+        CHK(dev_alloc(m, &m->dec2_partial, (size_t)3 * D * 2));
+        WQ4_CUDA(cudaMemset(m->dec2_partial, 0, (size_t)3 * D * 8));
         m->dec2_ready = true;
     }
     // first generation: only when it can be reached (second generation unavailable, or grouped batches asked for by an override)
