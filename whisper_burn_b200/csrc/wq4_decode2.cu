@@ -69,6 +69,10 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v)
 {
     asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
+__device__ __forceinline__ void st_cluster_b16(uint32_t addr, uint16_t v)
+{
+    asm volatile("st.shared::cluster.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
+}
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p)
 {
     unsigned v;
@@ -104,6 +108,47 @@ __device__ __forceinline__ void word_f32(uint32_t w, float (&f)[8])
     f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
 }
 
+// Activation vectors that feed a GEMV are kept in shared memory as f16 (like every tensor-core operand of this library;
+// the weights (nib - 8) are exact in f16) so that the products run on the sm_100 mixed-precision FMA (fma.rn.f32.f16 ->
+// SASS FHFMA: f16 x f16 + f32, exact product, f32 accumulation) with no half -> float conversion: 17 instructions per
+// 8 weights instead of 25.  Layout: 40 halfs (80 bytes) per block of 32, so that the eight lanes of a quarter-warp, which
+// read eight different blocks, hit eight different bank groups.
+__device__ __forceinline__ int hidx(int i) { return i + ((i >> 5) << 3); }
+__device__ __forceinline__ void fhfma2(float &acc_lo, float &acc_hi, uint32_t a2, uint32_t b2)      // (a.lo*b.lo, a.hi*b.hi)
+{
+    asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %2;\n\tmov.b32 {bl, bh}, %3;\n\t"
+        "fma.rn.f32.f16 %0, al, bl, %0;\n\tfma.rn.f32.f16 %1, ah, bh, %1;\n\t}"
+        : "+f"(acc_lo), "+f"(acc_hi) : "r"(a2), "r"(b2));
+}
+// sum_k (nib - 8) * x[k] over one 32-weight block; xh = the block's 32 activations as f16 (16-byte aligned)
+__device__ __forceinline__ float block_dot32_h(uint4 q, const __half *xh)
+{
+    const __half2 k1032 = __floats2half2_rn(1032.0f, 1032.0f);
+    const __half2 k16th = __floats2half2_rn(0.0625f, 0.0625f);
+    const __half2 km72 = __floats2half2_rn(-72.0f, -72.0f);
+    float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint4 xq = *reinterpret_cast<const uint4 *>(xh + c * 8);
+        uint32_t t0 = (w[c] & 0x000F000Fu) | 0x64006400u;
+        uint32_t t1 = (w[c] & 0x00F000F0u) | 0x64006400u;
+        const uint32_t w8 = w[c] >> 8;
+        uint32_t t2 = (w8 & 0x000F000Fu) | 0x64006400u;
+        uint32_t t3 = (w8 & 0x00F000F0u) | 0x64006400u;
+        const __half2 h0 = __hsub2(*reinterpret_cast<__half2 *>(&t0), k1032);               // (e0 - 8, e1 - 8), exact
+        const __half2 h1 = __hfma2(*reinterpret_cast<__half2 *>(&t1), k16th, km72);        // (e2 - 8, e3 - 8)
+        const __half2 h2 = __hsub2(*reinterpret_cast<__half2 *>(&t2), k1032);
+        const __half2 h3 = __hfma2(*reinterpret_cast<__half2 *>(&t3), k16th, km72);
+        fhfma2(s0, s1, *reinterpret_cast<const uint32_t *>(&h0), xq.x);
+        fhfma2(s2, s3, *reinterpret_cast<const uint32_t *>(&h1), xq.y);
+        fhfma2(s0, s1, *reinterpret_cast<const uint32_t *>(&h2), xq.z);
+        fhfma2(s2, s3, *reinterpret_cast<const uint32_t *>(&h3), xq.w);
+    }
+    return (s0 + s1) + (s2 + s3);
+}
+
+// (f32 form, kept for reference / the logits stage)
 // sum_k (nib - 8) * x[k] over one 32-weight block; xp = padded activation pointer of the block (16-byte aligned)
 __device__ __forceinline__ float block_dot32(uint4 q, const float *xp)
 {
@@ -122,9 +167,9 @@ __device__ __forceinline__ float block_dot32(uint4 q, const float *xp)
 }
 
 // One GEMV job of this CTA out of shared memory: y[r] = sum_k W[r][k] x[k], r < rows.  G lanes per row (power of two).
-//   nib : [rows_alloc][kb] uint4 row-major, scl : [rows_alloc][kb] f16;   xp : padded activation (pidx);   epi(r, y)
+//   nib : [rows_alloc][kb] uint4 row-major, scl : [rows_alloc][kb] f16;   xp : padded f16 activation (hidx);   epi(r, y)
 template <int G, typename Epi>
-__device__ __forceinline__ void gemv_job(const uint4 *nib, const __half *scl, int rows, int kb, const float *xp, Epi epi)
+__device__ __forceinline__ void gemv_job(const uint4 *nib, const __half *scl, int rows, int kb, const __half *xp, Epi epi)
 {
     constexpr int RPP = kT / G;
     const int g = threadIdx.x & (G - 1), rl = threadIdx.x / G;
@@ -135,7 +180,7 @@ __device__ __forceinline__ void gemv_job(const uint4 *nib, const __half *scl, in
             const uint4 *nr = nib + (size_t)r * kb;
             const __half *sr = scl + (size_t)r * kb;
 #pragma unroll 2
-            for (int k = g; k < kb; k += G) acc = fmaf(__half2float(sr[k]), block_dot32(nr[k], xp + k * 36), acc);
+            for (int k = g; k < kb; k += G) acc = fmaf(__half2float(sr[k]), block_dot32_h(nr[k], xp + k * 40), acc);
         }
 #pragma unroll
         for (int o = G >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -185,7 +230,8 @@ __device__ __forceinline__ void soft_key(Soft2 &st, const float (&qv)[8], uint4 
 }
 
 struct Smem2 {
-    float *xres, *xn, *qkvh, *atth, *hsl, *clp, *wpart, *red;
+    float *xres, *xn, *qkvh, *clp, *wpart, *red;
+    __half *xn16, *atth16, *hsl16;      // f16 operands of the GEMVs (hidx layout)
     uint64_t *bars;
     uint8_t *bufA, *bufB, *bufC, *bufKV;
 };
@@ -240,7 +286,7 @@ __device__ __forceinline__ void attn_exchange(Soft2 st, const Smem2 &s, int rank
             L += sc * s.clp[p * kPS + 65];
             o += sc * s.clp[p * kPS + tid];
         }
-        s.atth[pidx(tid)] = o / L;
+        s.atth16[hidx(tid)] = __ushort_as_half(f2h_sat2(o / L));
     }
     __syncthreads();
 }
@@ -256,50 +302,49 @@ __device__ __forceinline__ void attn_exchange(Soft2 st, const Smem2 &s, int rank
 // cleared in phase 1 of the next launch before phase 2 adds into it: no host-side memset per step.
 constexpr float kFixScale = 268435456.0f;            // 2^28
 constexpr float kFixInv = 1.0f / 268435456.0f;
-struct PhasePre { float bias[4]; float4 w, b; };     // per-thread values a phase needs right after the grid barrier, requested before it
+struct PhasePre { float4 bias, w, b; };              // per-thread values a phase needs right after the grid barrier, requested before it
 
 __device__ __forceinline__ void phase_prefetch(PhasePre &pp, const float *bias, const float *lnw, const float *lnb, int D)
 {
     const int tid = threadIdx.x;
-#pragma unroll
-    for (int i = 0; i < 4; i++) { const int c = tid + i * kT; pp.bias[i] = (bias && c < D) ? __ldg(bias + c) : 0.0f; }
-    pp.w = make_float4(0.f, 0.f, 0.f, 0.f); pp.b = pp.w;
-    if (tid < (D >> 2)) { pp.w = __ldg(reinterpret_cast<const float4 *>(lnw) + tid); pp.b = __ldg(reinterpret_cast<const float4 *>(lnb) + tid); }
+    pp.bias = make_float4(0.f, 0.f, 0.f, 0.f); pp.w = pp.bias; pp.b = pp.bias;
+    if (tid < (D >> 2)) {
+        if (bias) pp.bias = __ldg(reinterpret_cast<const float4 *>(bias) + tid);
+        pp.w = __ldg(reinterpret_cast<const float4 *>(lnw) + tid);
+        pp.b = __ldg(reinterpret_cast<const float4 *>(lnb) + tid);
+    }
 }
 
-// x <- x + bias + (accumulated partial sums of the previous phase), every CTA for the whole vector (D <= 4 * kT);
-// `clr` = this CTA's share of the vector to clear for the phase after next (null: nothing to clear)
-__device__ __forceinline__ void reduce_x(const long long *acc, const PhasePre &pp, const Smem2 &s, int D, long long *clr, int n_cta)
-{
-    const int tid = threadIdx.x;
-    long long v[4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) { const int c = tid + i * kT; v[i] = c < D ? __ldcg(acc + c) : 0ll; }
-    if (clr)
-        for (int c = (int)blockIdx.x * kT + tid; c < D; c += n_cta * kT) clr[c] = 0ll;
-#pragma unroll
-    for (int i = 0; i < 4; i++) { const int c = tid + i * kT; if (c < D) s.xres[c] += pp.bias[i] + __ll2float_rn(v[i]) * kFixInv; }
-    __syncthreads();
-}
-__device__ __forceinline__ void acc_add(long long *acc, float y)
-{
-    atomicAdd(reinterpret_cast<unsigned long long *>(acc), (unsigned long long)__float2ll_rn(y * kFixScale));
-}
-
-// LayerNorm::forward (src/model/layers.rs:23-31) of xres -> xn (padded); D % 4 == 0, D <= 4 * kT
-__device__ __forceinline__ void ln_to_xn(const PhasePre &pp, const Smem2 &s, int D)
+// x <- x + bias + (accumulated partial sums of the previous phase; acc == null: none), then LayerNorm::forward
+// (src/model/layers.rs:23-31, two-pass as the reference) of x -> xn (f32, padded) and xn16 (f16 operand of the GEMVs).
+// Every CTA does the whole vector: thread t owns columns 4t..4t+3 from the accumulator read to the normalised store, so
+// the only block-wide synchronisations are the two statistics and the final hand-over.  D % 4 == 0, D <= 4 * kT.
+// `clr` = the accumulator vector to clear for the phase after next (this CTA's share), or null.
+__device__ __forceinline__ void reduce_ln(const long long *acc, const PhasePre &pp, const Smem2 &s, int D, long long *clr, int n_cta)
 {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const bool on = tid < (D >> 2);
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4 ww = pp.w, bb = pp.b;
-    if (on) v = reinterpret_cast<const float4 *>(s.xres)[tid];
-    float sum = warp_sum2((v.x + v.y) + (v.z + v.w));
+    if (on) {
+        v = reinterpret_cast<const float4 *>(s.xres)[tid];
+        if (acc) {
+            const longlong2 a0 = __ldcg(reinterpret_cast<const longlong2 *>(acc) + 2 * tid);
+            const longlong2 a1 = __ldcg(reinterpret_cast<const longlong2 *>(acc) + 2 * tid + 1);
+            v.x += pp.bias.x + __ll2float_rn(a0.x) * kFixInv;
+            v.y += pp.bias.y + __ll2float_rn(a0.y) * kFixInv;
+            v.z += pp.bias.z + __ll2float_rn(a1.x) * kFixInv;
+            v.w += pp.bias.w + __ll2float_rn(a1.y) * kFixInv;
+            reinterpret_cast<float4 *>(s.xres)[tid] = v;
+        }
+    }
+    if (clr)
+        for (int c = (int)blockIdx.x * kT + tid; c < D; c += n_cta * kT) clr[c] = 0ll;
+    const float sum = warp_sum2((v.x + v.y) + (v.z + v.w));
     if (lane == 0) s.red[warp] = sum;
     __syncthreads();
     float tot = 0.0f;
 #pragma unroll
-    for (int i = 0; i < kT / 32; i++) tot += s.red[i];
+    for (int i = 0; i < kT / 32; i += 4) { const float4 t = *reinterpret_cast<const float4 *>(s.red + i); tot += (t.x + t.y) + (t.z + t.w); }
     const float mean = tot / (float)D;
     float q = 0.0f;
     if (on) { v.x -= mean; v.y -= mean; v.z -= mean; v.w -= mean; q = (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w); }
@@ -308,12 +353,21 @@ __device__ __forceinline__ void ln_to_xn(const PhasePre &pp, const Smem2 &s, int
     __syncthreads();
     float vt = 0.0f;
 #pragma unroll
-    for (int i = 0; i < kT / 32; i++) vt += s.red[32 + i];
+    for (int i = 0; i < kT / 32; i += 4) { const float4 t = *reinterpret_cast<const float4 *>(s.red + 32 + i); vt += (t.x + t.y) + (t.z + t.w); }
     const float inv = 1.0f / sqrtf(vt / (float)D + 1e-5f);
-    if (on)
-        *reinterpret_cast<float4 *>(s.xn + pidx(tid * 4)) = make_float4(v.x * inv * ww.x + bb.x, v.y * inv * ww.y + bb.y,
-                                                                        v.z * inv * ww.z + bb.z, v.w * inv * ww.w + bb.w);
+    if (on) {
+        const float4 o = make_float4(v.x * inv * pp.w.x + pp.b.x, v.y * inv * pp.w.y + pp.b.y, v.z * inv * pp.w.z + pp.b.z, v.w * inv * pp.w.w + pp.b.w);
+        *reinterpret_cast<float4 *>(s.xn + pidx(tid * 4)) = o;                              // f32 copy: the logits stage
+        uint2 pk;
+        pk.x = (uint32_t)f2h_sat2(o.x) | ((uint32_t)f2h_sat2(o.y) << 16);
+        pk.y = (uint32_t)f2h_sat2(o.z) | ((uint32_t)f2h_sat2(o.w) << 16);
+        *reinterpret_cast<uint2 *>(s.xn16 + hidx(tid * 4)) = pk;                            // f16 copy: the GEMVs
+    }
     __syncthreads();
+}
+__device__ __forceinline__ void acc_add(long long *acc, float y)
+{
+    atomicAdd(reinterpret_cast<unsigned long long *>(acc), (unsigned long long)__float2ll_rn(y * kFixScale));
 }
 
 __device__ __forceinline__ void grid_arrive(unsigned *counter)
@@ -344,12 +398,13 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
     s.xres = reinterpret_cast<float *>(sm_raw);
     s.xn = s.xres + D;
     s.qkvh = s.xn + Dp;
-    s.atth = s.qkvh + 192;
-    s.hsl = s.atth + 72;
-    s.clp = s.hsl + 288;
+    s.clp = s.qkvh + 192;
     s.wpart = s.clp + kMaxCS * kPS;
     s.red = s.wpart + (kT / 32) * kPS;
     s.bars = reinterpret_cast<uint64_t *>(s.red + 64);
+    s.xn16 = reinterpret_cast<__half *>(s.bars + 4);
+    s.atth16 = s.xn16 + (D >> 5) * 40;
+    s.hsl16 = s.atth16 + 2 * 40;
     s.bufA = sm_raw + a.off_bufA;
     s.bufB = s.bufA + a.sA;
     s.bufC = s.bufB + a.sB;
@@ -438,10 +493,9 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
             STAMP();
             STAMP2(1);
-            reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
         }
         STAMP2(2);
-        ln_to_xn(pp, s, D);
+        reduce_ln(l > 0 ? accv + (size_t)((ph + 2) % 3) * D : nullptr, pp, s, D, l > 0 ? accv + (size_t)((ph + 1) % 3) * D : nullptr, n_cta);
         STAMP2(3);
         wait_bar(barA, par);
         STAMP2(4);
@@ -450,9 +504,12 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             const __half *scl = reinterpret_cast<const __half *>(s.bufA + a.a_scl1);
             const int vr0 = rank * a.rq, rows = max(0, min(192, vr0 + a.rq) - vr0);
             const uint32_t qb = ptx::smem_u32(s.qkvh);
-            gemv_job<16>(nib, scl, rows, kbD, s.xn, [&](int r, float y) {
+            // the row's bias is requested before the weight loop (one pass when rows <= kT / 16: every CTA of a Large-V3 cluster)
+            const int pr = vr0 + tid / 16;
+            const float pre_b = (L.b_qkv && pr < 192) ? __ldg(L.b_qkv + (pr >> 6) * D + cl * 64 + (pr & 63)) : 0.0f;
+            gemv_job<16>(nib, scl, rows, kbD, s.xn16, [&](int r, float y) {
                 const int vr = vr0 + r, kind = vr >> 6;
-                if (L.b_qkv) y += __ldg(L.b_qkv + kind * D + cl * 64 + (vr & 63));
+                if (L.b_qkv) y += (r < kT / 16) ? pre_b : __ldg(L.b_qkv + kind * D + cl * 64 + (vr & 63));
                 for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(qb + vr * 4, p), y);
             });
         }
@@ -501,7 +558,7 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             const __half *scl = reinterpret_cast<const __half *>(s.bufA + a.a_scl2);
             const int n0 = rank * a.ro, rows = max(0, min(D, n0 + a.ro) - n0);
             long long *dst = accv + (size_t)(ph++ % 3) * D + n0;
-            gemv_job<2>(nib, scl, rows, 2, s.atth, [&](int r, float y) { acc_add(dst + r, y); });
+            gemv_job<2>(nib, scl, rows, 2, s.atth16, [&](int r, float y) { acc_add(dst + r, y); });
         }
         STAMP2(9);
         grid_arrive(a.barrier);
@@ -514,9 +571,8 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
         grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
         STAMP();
         STAMP2(11);
-        reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
         STAMP2(12);
-        ln_to_xn(pp, s, D);
+        reduce_ln(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
         STAMP2(13);
         wait_bar(barB, par);
         STAMP2(14);
@@ -525,9 +581,11 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             const __half *scl = reinterpret_cast<const __half *>(s.bufB + a.b_scl1);
             const int vr0 = rank * a.rc, rows = max(0, min(64, vr0 + a.rc) - vr0);
             const uint32_t qb = ptx::smem_u32(s.qkvh);
-            gemv_job<32>(nib, scl, rows, kbD, s.xn, [&](int r, float y) {
+            const int pr = vr0 + tid / 32;
+            const float pre_b = (L.b_cq && pr < 64) ? __ldg(L.b_cq + cl * 64 + pr) : 0.0f;
+            gemv_job<32>(nib, scl, rows, kbD, s.xn16, [&](int r, float y) {
                 const int vr = vr0 + r;
-                if (L.b_cq) y += __ldg(L.b_cq + cl * 64 + vr);
+                if (L.b_cq) y += (r < kT / 32) ? pre_b : __ldg(L.b_cq + cl * 64 + vr);
                 for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(qb + vr * 4, p), y);
             });
         }
@@ -566,7 +624,7 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             const __half *scl = reinterpret_cast<const __half *>(s.bufB + a.b_scl2);
             const int n0 = rank * a.ro, rows = max(0, min(D, n0 + a.ro) - n0);
             long long *dst = accv + (size_t)(ph++ % 3) * D + n0;
-            gemv_job<2>(nib, scl, rows, 2, s.atth, [&](int r, float y) { acc_add(dst + r, y); });
+            gemv_job<2>(nib, scl, rows, 2, s.atth16, [&](int r, float y) { acc_add(dst + r, y); });
         }
         STAMP2(19);
         grid_arrive(a.barrier);
@@ -579,9 +637,8 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
         grid_wait(a.barrier, ++n_sync * n_cta, a.dev_err);
         STAMP();
         STAMP2(21);
-        reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
         STAMP2(22);
-        ln_to_xn(pp, s, D);
+        reduce_ln(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
         STAMP2(23);
         wait_bar(barC, par);
         STAMP2(24);
@@ -589,13 +646,16 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             const uint4 *nib = reinterpret_cast<const uint4 *>(s.bufC);
             const __half *scl = reinterpret_cast<const __half *>(s.bufC + a.c_scl1);
             const int vr0 = rank * a.rf, rows = max(0, min(256, vr0 + a.rf) - vr0);
-            const uint32_t hb = ptx::smem_u32(s.hsl);
-            gemv_job<8>(nib, scl, rows, kbD, s.xn, [&](int r, float y) {
+            const uint32_t hb = ptx::smem_u32(s.hsl16);
+            const int pr = vr0 + tid / 8;
+            const float pre_b = (L.b_fc1 && pr < 256) ? __ldg(L.b_fc1 + cl * 256 + pr) : 0.0f;
+            gemv_job<8>(nib, scl, rows, kbD, s.xn16, [&](int r, float y) {
                 const int vr = vr0 + r;
-                if (L.b_fc1) y += __ldg(L.b_fc1 + cl * 256 + vr);
+                if (L.b_fc1) y += (r < kT / 8) ? pre_b : __ldg(L.b_fc1 + cl * 256 + vr);
                 y = wq4_gelu_tanh(y);
-                const uint32_t off = (uint32_t)pidx(vr) * 4u;
-                for (int p = 0; p < CS; p++) st_cluster_f32(ptx::mapa_u32(hb + off, p), y);
+                const uint32_t off = (uint32_t)hidx(vr) * 2u;
+                const uint16_t yh = f2h_sat2(y);
+                for (int p = 0; p < CS; p++) st_cluster_b16(ptx::mapa_u32(hb + off, p), yh);
             });
         }
         STAMP2(25);
@@ -607,7 +667,7 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
             const __half *scl = reinterpret_cast<const __half *>(s.bufC + a.c_scl2);
             const int n0 = rank * a.ro, rows = max(0, min(D, n0 + a.ro) - n0);
             long long *dst = accv + (size_t)(ph++ % 3) * D + n0;
-            gemv_job<8>(nib, scl, rows, 8, s.hsl, [&](int r, float y) { acc_add(dst + r, y); });
+            gemv_job<8>(nib, scl, rows, 8, s.hsl16, [&](int r, float y) { acc_add(dst + r, y); });
         }
         STAMP2(27);
         grid_arrive(a.barrier);
@@ -626,8 +686,7 @@ __global__ void __launch_bounds__(kT, 1) decode2_kernel(const Dec2Args a)
         // reads vector 2 and clears vector 1 (read in the last phase); vector 0 was cleared in the last phase, vector 2 is
         // cleared in phase 1 of the next launch, before phase 2 adds into it
         long long *const accv = reinterpret_cast<long long *>(a.partial);
-        reduce_x(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
-        ln_to_xn(pp, s, D);
+        reduce_ln(accv + (size_t)((ph + 2) % 3) * D, pp, s, D, accv + (size_t)((ph + 1) % 3) * D, n_cta);
     }
     const int V = a.V, Vp = a.Vp, chunks = D >> 3;
     const bool pick = a.arg_hi > a.arg_lo && a.next_out != nullptr;
@@ -760,8 +819,9 @@ static void dec2_geometry(Dec2Args &a, int D, int F, int H, int T_enc, int CS)
     a.c_scl2 = a.c_nib2 + up16((size_t)a.ro * 8 * 16);
     a.sC = up128(a.c_scl2 + up16((size_t)a.ro * 8 * 2));
     const int Dp = D / 32 * 36;
-    const size_t floats = (size_t)D + Dp + 192 + 72 + 288 + kMaxCS * kPS + (kT / 32) * kPS + 64;
-    a.off_bufA = up128(floats * 4 + 4 * 8);
+    const size_t floats = (size_t)D + Dp + 192 + kMaxCS * kPS + (kT / 32) * kPS + 64;
+    const size_t halfs = (size_t)(D / 32 + 2 + 8) * 40;
+    a.off_bufA = up128(floats * 4 + 4 * 8 + halfs * 2);
 }
 
 static size_t dec2_smem_bytes(const Dec2Args &a) { return (size_t)a.off_bufA + a.sA + a.sB + a.sC + up128((size_t)a.kpc * 256); }
