@@ -28,9 +28,10 @@ def main():
     ap.add_argument("csv")
     ap.add_argument("--skip", type=int, default=0, help="ignore the first N launches (warm-up)")
     ap.add_argument("--take", type=int, default=0, help="use only M launches after the skip (0 = all)")
+    ap.add_argument("--last", type=int, default=0, help="use only the last M launches (one steady-state step)")
     ap.add_argument("--traffic-key", default="")
     ap.add_argument("--traffic-json", default="profiles/traffic.json")
-    ap.add_argument("--gemm-regex", default=r"q4_gemm2?_kernel")
+    ap.add_argument("--gemm-regex", default=r"q4_(gemm2|chain)_kernel")
     a = ap.parse_args()
 
     rows = defaultdict(dict)
@@ -47,6 +48,8 @@ def main():
     ids = sorted(rows)[a.skip:]
     if a.take:
         ids = ids[: a.take]
+    if a.last:
+        ids = ids[-a.last:]
     fam = OrderedDict()
     for i in ids:
         d = rows[i]
