@@ -134,6 +134,7 @@ extern "C" {
     pub fn wq4_linear_plan(w: *const wq4_tensor, rows: i64, flags: u32, tile_m: *mut i32) -> i32;
     pub fn wq4_launch_count() -> i64;
     pub fn wq4_launch_count_reset();
+    pub fn wq4_debug_f16_overflow_count(device: i32, reset: i32) -> i64;
     pub fn wq4_device_error_flag(device: i32) -> i32;
     pub fn wq4_profile_enable(on: i32);
     pub fn wq4_profile_reset();

@@ -249,6 +249,9 @@ WQ4_API void wq4_launch_count_reset(void);
 WQ4_API void wq4_profile_enable(int32_t on);
 WQ4_API void wq4_profile_reset(void);
 WQ4_API int32_t wq4_profile_read(int32_t kind, int64_t *launches, double *ms, double *work);
+/* Debug builds only (csrc/build.sh -DWQ4_DEBUG_OVERFLOW): number of f32 activations the drop-in entry points clipped to
+ * +-65504 when converting to the f16 tensor-core operand (cvt.rn.satfinite) since the last reset; -1 in release builds. */
+WQ4_API int64_t wq4_debug_f16_overflow_count(int32_t device, int32_t reset);
 /* Sticky device-side error flag set by kernels (pipeline wait timeouts); 0 = clean. */
 WQ4_API int32_t wq4_device_error_flag(int32_t device);
 

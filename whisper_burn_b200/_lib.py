@@ -91,6 +91,8 @@ def lib() -> C.CDLL:
     L.wq4_launch_count.restype = i64
     L.wq4_launch_count_reset.restype = None
     L.wq4_device_error_flag.argtypes = [i32]
+    L.wq4_debug_f16_overflow_count.argtypes = [i32, i32]
+    L.wq4_debug_f16_overflow_count.restype = i64
     for name in dir(L):
         pass
     for fn in ("wq4_tensor_create", "wq4_tensor_destroy", "wq4_tensor_shape", "wq4_tensor_device",

@@ -83,7 +83,20 @@ int wq4_sm_count(int device)
 }
 
 // ---- small kernels -----------------------------------------------------------------------------
+// Debug builds (build.sh -DWQ4_DEBUG_OVERFLOW): the f32 -> f16 conversion of the drop-in entry points counts the
+// activations it clips to +-65504 (cvt.rn.satfinite), SURVEY 7-B.  Release builds carry no counter code.
+__device__ unsigned long long g_f16_overflows = 0ull;
+
 namespace {
+
+__device__ __forceinline__ void count_overflow(float v)
+{
+#ifdef WQ4_DEBUG_OVERFLOW
+    if (fabsf(v) > 65504.0f) atomicAdd(&g_f16_overflows, 1ull);
+#else
+    (void)v;
+#endif
+}
 
 template <bool kBF16>
 __global__ void cvt_f32_to_16_kernel(const float4 *__restrict__ src, uint2 *__restrict__ dst, int64_t n4,
@@ -100,6 +113,7 @@ __global__ void cvt_f32_to_16_kernel(const float4 *__restrict__ src, uint2 *__re
             o.y = *reinterpret_cast<uint32_t *>(&b);
         } else {
             // saturating: activations beyond the f16 range clamp to +-65504 instead of inf
+            count_overflow(v.x); count_overflow(v.y); count_overflow(v.z); count_overflow(v.w);
             asm("{.reg .b16 l, h; cvt.rn.satfinite.f16.f32 l, %1; cvt.rn.satfinite.f16.f32 h, %2; mov.b32 %0, {l, h};}"
                 : "=r"(o.x) : "f"(v.x), "f"(v.y));
             asm("{.reg .b16 l, h; cvt.rn.satfinite.f16.f32 l, %1; cvt.rn.satfinite.f16.f32 h, %2; mov.b32 %0, {l, h};}"
@@ -268,6 +282,20 @@ int32_t wq4_profile_read(int32_t kind, int64_t *launches, double *ms, double *wo
     if (ms) *ms = t;
     if (work) *work = w;
     return WQ4_OK;
+}
+
+int64_t wq4_debug_f16_overflow_count(int32_t device, int32_t reset)
+{
+#ifdef WQ4_DEBUG_OVERFLOW
+    DeviceGuard g(device);
+    unsigned long long v = 0ull, z = 0ull;
+    if (!g.ok || cudaMemcpyFromSymbol(&v, g_f16_overflows, sizeof(v)) != cudaSuccess) { cudaGetLastError(); return -2; }
+    if (reset) cudaMemcpyToSymbol(g_f16_overflows, &z, sizeof(z));
+    return (int64_t)v;
+#else
+    (void)device; (void)reset;
+    return -1;      // not a debug build
+#endif
 }
 
 int32_t wq4_device_error_flag(int32_t device)

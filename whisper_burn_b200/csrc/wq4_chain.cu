@@ -469,7 +469,7 @@ q4_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ 
             const int t0 = rb * TILE_M;
             const uint32_t buf = ft & 1u;
             mbar_wait(bar_stat_empty(buf), ((ft >> 1) & 1u) ^ 1u, cta_abort, p.dev_err, 213);
-            dep_wait(p.counters + (size_t)(P.dep * p.mtiles + rb) * kCtrStride, (unsigned)P.dep_count, lane, cta_abort, p.dev_err, 214);
+            if (P.dep >= 0) dep_wait(p.counters + (size_t)(P.dep * p.mtiles + rb) * kCtrStride, (unsigned)P.dep_count, lane, cta_abort, p.dev_err, 214);
             const int G = P.stats_groups;
             // tiles of this role are numbered like the epilogue's: count every tile
             CH_TL(tile_it, 10);
@@ -548,13 +548,14 @@ q4_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ 
             const float *res = P.residual;
             const int rows = p.rows;
             // epilogue mode of the problem (warp-uniform): 0 residual + f32 + scaled f16 + statistics (out-proj, fc2),
-            // 1 residual + f32 (last fc2), 2 fold + GELU + f16 (fc1), 3 fold + f16 (q|k|v), 4 f16, 5 generic
+            // 1 residual + f32 (last fc2), 2 fold + GELU + f16 (fc1), 3 fold + f16 (q|k|v), 4 f16, 6 fold + f32, 5 generic
             int mode = 5;
             if (!fold && !P.gelu && res && P.y32 && P.y16 && P.stats_out) mode = 0;
             else if (!fold && !P.gelu && res && P.y32 && !P.y16 && !P.stats_out) mode = 1;
             else if (fold && P.gelu && !res && !P.y32 && P.y16 && !P.stats_out) mode = 2;
             else if (fold && !P.gelu && !res && !P.y32 && P.y16 && !P.stats_out) mode = 3;
             else if (!fold && !P.gelu && !res && !P.y32 && P.y16 && !P.stats_out) mode = 4;
+            else if (fold && !P.gelu && !res && P.y32 && !P.y16 && !P.stats_out) mode = 6;      // decoder q|k|v / cross-q: f32 for the attention kernel
             // the producer's stores (residual stream) are acquired by this warp itself, not only through the
             // X producer -> TMA -> MMA -> accumulator barrier chain
             float4 r4[8];
@@ -601,6 +602,7 @@ q4_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ 
                 case 2: epi_chunk_t<true, true, false, false, true, false>(tr, stat + c0, T, r4, tb, nvalid, lane, sp, q, 1 + eh); break;
                 case 3: epi_chunk_t<true, false, false, false, true, false>(tr, stat + c0, T, r4, tb, nvalid, lane, sp, q, 1 + eh); break;
                 case 4: epi_chunk_t<false, false, false, false, true, false>(tr, stat + c0, T, r4, tb, nvalid, lane, sp, q, 1 + eh); break;
+                case 6: epi_chunk_t<true, false, false, true, false, false>(tr, stat + c0, T, r4, tb, nvalid, lane, sp, q, 1 + eh); break;
                 default: {
                     // any other combination: the general form, one row group at a time
                     const bool f_gelu = P.gelu != 0;
@@ -760,7 +762,7 @@ int32_t wq4_launch_chain(const ChainGemm *g, int n, int64_t rows, unsigned *coun
         if (g[i].dep >= i) { wq4_set_error("chain: problem %d depends on a later problem", i); return WQ4_ERR_INVALID; }
         if (w->n % 4 != 0 || (g[i].stats_out && w->n % 128 != 0)) { wq4_set_error("chain: N must be a multiple of 4 (128 with statistics)"); return WQ4_ERR_SHAPE; }
         if (g[i].stats_out && !(g[i].residual && g[i].y32 && g[i].y16 && !g[i].cvec && !(g[i].flags & WQ4_EPI_GELU))) { wq4_set_error("chain: statistics are produced by the residual epilogue only"); return WQ4_ERR_INVALID; }
-        if (g[i].cvec && (g[i].dep < 0 || !g[i].stats_in || g[i].stats_groups < 1 || g[i].stats_groups > kMaxGroups)) { wq4_set_error("chain: problem %d folds a LayerNorm without a producer", i); return WQ4_ERR_INVALID; }
+        if (g[i].cvec && (!g[i].stats_in || g[i].stats_groups < 1 || g[i].stats_groups > kMaxGroups)) { wq4_set_error("chain: problem %d folds a LayerNorm without a producer", i); return WQ4_ERR_INVALID; }
         cuuint64_t dims[3] = {(cuuint64_t)w->k, (cuuint64_t)rows, 1};
         cuuint64_t strides[2] = {(cuuint64_t)w->k * 2, (cuuint64_t)w->k * 2 * (cuuint64_t)rows};
         cuuint32_t box[3] = {64u, (cuuint32_t)(tile_m / 2), 1};

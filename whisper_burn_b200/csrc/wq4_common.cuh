@@ -139,7 +139,7 @@ int wq4_gemm_cluster_size(int64_t np);
 // Chain of Q4 GEMMs in one persistent launch with row-block dependencies and the LayerNorm between two of them folded
 // into the consumer's epilogue (wq4_chain.cu).  Problem i reads x16 [rows][K_i] f16 and may depend on problem dep < i
 // (its x16 / residual / stats_in are that problem's outputs); dep = -1: inputs come from the predecessor kernel.
-#define WQ4_CHAIN_MAX 5
+#define WQ4_CHAIN_MAX 8
 struct ChainGemm {
     const wq4_tensor *w;
     const float *bias;        // [N]: bias, or b' = bias + W.beta when cvec is given

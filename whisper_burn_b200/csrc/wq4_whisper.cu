@@ -154,7 +154,11 @@ struct EncLayer {
     // LayerNorm folded into the consumer GEMM (wq4_chain.cu): c = W.gamma, b' = bias + W.beta for q|k|v (attn_ln) and fc1 (mlp_ln)
     float *qkv_c = nullptr, *qkv_b2 = nullptr, *fc1_c = nullptr, *fc1_b2 = nullptr;
 };
-struct DecLayer { LNp attn_ln; Lin qkv, out; LNp cross_ln; Lin cq, ckv, cout; LNp mlp_ln; Lin fc1, fc2; };
+struct DecLayer {
+    LNp attn_ln; Lin qkv, out; LNp cross_ln; Lin cq, ckv, cout; LNp mlp_ln; Lin fc1, fc2;
+    // LayerNorm fold vectors of the chained decode step (wq4_chain.cu): c = W.gamma, b' = bias + W.beta
+    float *qkv_c = nullptr, *qkv_b2 = nullptr, *cq_c = nullptr, *cq_b2 = nullptr, *fc1_c = nullptr, *fc1_b2 = nullptr;
+};
 
 }  // namespace
 
@@ -182,6 +186,8 @@ struct wq4_whisper {
     float2 *ln_stats_a = nullptr, *ln_stats_b = nullptr;   // [D/128][rows] row partials of the residual stream (wq4_chain.cu)
     unsigned *chain_ctr = nullptr;                         // row-block arrival counters of the chain launches, zero between launches
     bool chain_ready = false;
+    float2 *dln_stats_a = nullptr, *dln_stats_b = nullptr; // the same for the decoder's chained steps: [D/128][max_batch * max_q]
+    unsigned *dchain_ctr = nullptr;
     int64_t Cp1 = 0, Tp1 = 0, Tp2 = 0;
     // decoder state
     __half *cross_kv = nullptr;      // [L][B][H][T_enc][128]: head-major, 64 K | 64 V per key
@@ -220,6 +226,34 @@ namespace {
         if (s__ != WQ4_OK) return s__;    \
     } while (0)
 
+static int decode_chain_mode();
+static bool decode_chain_enabled() { return decode_chain_mode() != 0; }
+static int decode_chain_mode()
+{
+    // The chain kernel on decode steps of 17+ clips, measured on Large-V3 at 32 clips (3.50 ms with the tcgen05 GEMM + LayerNorm
+    // launches, the default, mode 0):  2 = the linears between two attention kernels in ONE launch: 3.87 ms;  1 = one launch
+    // per linear with the LayerNorm folded into the consumer's epilogue (no LayerNorm launches): 4.00 ms.  With <= 64 rows
+    // every tile is a serial walk over K, so a dependent hop inside a launch costs what a PDL launch boundary costs, and the
+    // 640-thread, 128-row-tile kernel has ~5 us more fixed cost per launch than q4_gemm2_kernel<64>.  Kept for A/B runs.
+    static const int v = [] { const char *e = getenv("WQ4_DECODE_CHAIN"); return e ? atoi(e) : 0; }();
+    return v;
+}
+static int decode_chain_fc2_pieces()
+{
+    static const int v = [] { const char *e = getenv("WQ4_DECODE_CHAIN_FC2"); int r = e ? atoi(e) : 1; return r < 1 ? 1 : r > 4 ? 4 : r; }();
+    return decode_chain_mode() == 2 ? v : 1;
+}
+// mode 2: one launch; mode 1: one launch per problem (inputs then come from the predecessor kernel: dep = -1)
+static int32_t launch_chain_maybe_split(ChainGemm *g, int n, int64_t rows, unsigned *ctr, int tm, cudaStream_t st)
+{
+    if (decode_chain_mode() == 2) return wq4_launch_chain(g, n, rows, ctr, tm, st);
+    for (int i = 0; i < n; i++) {
+        g[i].dep = -1; g[i].edep_plus1 = 0;
+        int32_t s_ = wq4_launch_chain(g + i, 1, rows, ctr, tm, st);
+        if (s_ != WQ4_OK) return s_;
+    }
+    return WQ4_OK;
+}
 static bool chain_split_k()
 {
     // off by default: measured neutral at one Medium clip (2.166 against 2.148 ms per encoder pass): the extra tile epilogues cost what the shorter critical path saves
@@ -328,6 +362,20 @@ int32_t load_conv(wq4_whisper *m, const Gguf &g, const std::string &pfx, wq4_con
     return WQ4_OK;
 }
 
+// c = W.gamma and b' = bias + W.beta of a LayerNorm folded into the linear that consumes it (wq4_chain.cu), by the f32 GEMV
+int32_t ln_fold_vectors(wq4_whisper *m, const Lin &l, const LNp &ln, float **c_out, float **b_out)
+{
+    int64_t n, k;
+    wq4_tensor_shape(l.w, &n, &k);
+    CHK(dev_alloc(m, c_out, (size_t)n));
+    CHK(dev_alloc(m, b_out, (size_t)n));
+    LinearArgs a = {};
+    a.w = l.w; a.bias = nullptr; a.x_f32 = ln.w; a.y_f32 = *c_out; a.rows = 1; a.stream = nullptr;
+    CHK(wq4_launch_gemv(a));
+    a.bias = l.bias; a.x_f32 = ln.b; a.y_f32 = *b_out;
+    return wq4_launch_gemv(a);
+}
+
 int32_t load_model(wq4_whisper *m, const Gguf &g)
 {
     const wq4_whisper_config &c = m->cfg;
@@ -363,20 +411,9 @@ int32_t load_model(wq4_whisper *m, const Gguf &g)
     // LayerNorm fold vectors of the chained encoder block (wq4_chain.cu), f32 GEMV over the Q4 weights
     m->chain_ready = chain_enabled() && D % 128 == 0 && D <= 2048;
     if (m->chain_ready) {
-        auto fold = [&](const Lin &l, const LNp &ln, float **c_out, float **b_out) -> int32_t {
-            int64_t n, k;
-            wq4_tensor_shape(l.w, &n, &k);
-            CHK(dev_alloc(m, c_out, (size_t)n));
-            CHK(dev_alloc(m, b_out, (size_t)n));
-            LinearArgs a = {};
-            a.w = l.w; a.bias = nullptr; a.x_f32 = ln.w; a.y_f32 = *c_out; a.rows = 1; a.stream = nullptr;
-            CHK(wq4_launch_gemv(a));
-            a.bias = l.bias; a.x_f32 = ln.b; a.y_f32 = *b_out;
-            return wq4_launch_gemv(a);
-        };
         for (auto &L : m->enc) {
-            CHK(fold(L.qkv, L.attn_ln, &L.qkv_c, &L.qkv_b2));
-            CHK(fold(L.fc1, L.mlp_ln, &L.fc1_c, &L.fc1_b2));
+            CHK(ln_fold_vectors(m, L.qkv, L.attn_ln, &L.qkv_c, &L.qkv_b2));
+            CHK(ln_fold_vectors(m, L.fc1, L.mlp_ln, &L.fc1_c, &L.fc1_b2));
         }
         WQ4_CUDA(cudaDeviceSynchronize());
     }
@@ -406,7 +443,16 @@ int32_t load_model(wq4_whisper *m, const Gguf &g)
         CHK(load_q4_fused(m, g, {p + ".mlp.0"}, &L.fc1));
         CHK(load_q4_fused(m, g, {p + ".mlp.2"}, &L.fc2));
     }
-    return load_ln(m, g, "decoder.ln", &m->ln, D);                         // loader.rs:369
+    CHK(load_ln(m, g, "decoder.ln", &m->ln, D));                           // loader.rs:369
+    if (m->chain_ready) {
+        for (auto &L : m->dec) {
+            CHK(ln_fold_vectors(m, L.qkv, L.attn_ln, &L.qkv_c, &L.qkv_b2));
+            CHK(ln_fold_vectors(m, L.cq, L.cross_ln, &L.cq_c, &L.cq_b2));
+            CHK(ln_fold_vectors(m, L.fc1, L.mlp_ln, &L.fc1_c, &L.fc1_b2));
+        }
+        WQ4_CUDA(cudaDeviceSynchronize());
+    }
+    return WQ4_OK;
 }
 
 // Weight-derived decoder buffers, built once (the first reserve): decode-layout copies of the decoder linears for the
@@ -522,6 +568,13 @@ int32_t reserve(wq4_whisper *m, int64_t B)
     CHK(ws_alloc(m, &m->dxn16, (size_t)R * D));
     CHK(ws_alloc(m, &m->datt16, (size_t)R * D));
     CHK(ws_alloc(m, &m->dh16, (size_t)R * F));
+    if (m->chain_ready) {
+        CHK(ws_alloc(m, &m->dln_stats_a, (size_t)(D / 128) * R));
+        CHK(ws_alloc(m, &m->dln_stats_b, (size_t)(D / 128) * R));
+        const size_t words = wq4_chain_counter_words(R);
+        CHK(ws_alloc(m, &m->dchain_ctr, words));
+        WQ4_CUDA(cudaMemset(m->dchain_ctr, 0, words * sizeof(unsigned)));
+    }
     CHK(ws_alloc(m, &m->logits, (size_t)B * m->V));
     CHK(ws_alloc(m, &m->d_tokens, (size_t)R));
     CHK(ws_alloc(m, &m->d_next, (size_t)B));
@@ -778,7 +831,64 @@ int32_t decoder_pass(wq4_whisper *m, int64_t B, int64_t q_len, int64_t emb_pos0,
     const int64_t KB = m->kv_batch, M = KB * m->T_enc;          // layer strides of the caches
     if (q_len > m->max_q || kv_pos0 + q_len > ctx || emb_pos0 + q_len > ctx) { wq4_set_error("decoder_pass: context overflow"); return WQ4_ERR_INVALID; }
     CHK(wq4m_embed(m->d_tokens, m->tok_emb, m->dec_pos, m->dx, B, q_len, D, emb_pos0, st));
-    for (size_t l = 0; l < m->dec.size(); l++) {
+    // Single-query steps beyond the skinny kernel's reach (17+ clips): two chained launches per layer (wq4_chain.cu) --
+    // out-proj(+x) -> [cross LN folded] cross-q, and cross-out(+x) -> [mlp LN] fc1+GELU -> fc2(+x) -> [next attn LN] q|k|v --
+    // instead of six GEMM and three LayerNorm launches that each walk K serially on 10-40 SMs.
+    const bool chained = m->chain_ready && m->dchain_ctr && q_len == 1 && m->da_part && R >= decode_f16_min_rows() &&
+                         !(R <= skinny_step_rows() && use_skinny_step()) && decode_chain_enabled() && !m->dec.empty();
+    if (chained) {
+        const int groups = (int)(D / 128), tm = 128;
+        CHK(wq4m_layernorm(m->dx, m->dec[0].attn_ln.w, m->dec[0].attn_ln.b, nullptr, m->dxn16, R, D, st));
+        CHK(lin16(m->dec[0].qkv, m->dxn16, m->dqkv, nullptr, nullptr, R, 0, st));
+        for (size_t l = 0; l < m->dec.size(); l++) {
+            const DecLayer &L = m->dec[l];
+            const DecLayer *N = l + 1 < m->dec.size() ? &m->dec[l + 1] : nullptr;
+            __half *sk = m->self_k + l * (size_t)KB * ctx * D, *sv = m->self_v + l * (size_t)KB * ctx * D;
+            const __half *ck = m->cross_kv + l * (size_t)M * 2 * D;
+            CHK(wq4m_dec_attention_split(m->dqkv, 3 * D, sk, sv, D, ctx * D, 64, m->datt, m->datt16, D, B, H, kv_pos0 + 1,
+                                         m->da_part, m->da_part_floats, m->da_cnt, m->device, st, D, slot));
+            {
+                ChainGemm g[2] = {};
+                g[0].w = L.out.w; g[0].bias = L.out.bias; g[0].x16 = m->datt16; g[0].residual = m->dx; g[0].y32 = m->dx;
+                g[0].y16 = m->dxn16; g[0].y16_scale = L.cross_ln.w; g[0].stats_out = m->dln_stats_a; g[0].dep = -1;
+                g[1].w = L.cq.w; g[1].bias = L.cq_b2; g[1].cvec = L.cq_c; g[1].x16 = m->dxn16; g[1].y32 = m->dq;
+                g[1].stats_in = m->dln_stats_a; g[1].stats_groups = groups; g[1].dep = 0;
+                CHK(launch_chain_maybe_split(g, 2, R, m->dchain_ctr, tm, st));
+            }
+            CHK(wq4m_dec_attention_split(m->dq, D, ck, ck + 64, 128, m->T_enc * 2 * D, m->T_enc * 128, m->datt, m->datt16, D, B, H,
+                                         m->T_enc, m->da_part, m->da_part_floats, m->da_cnt, m->device, st, -1, slot));
+            {
+                ChainGemm g[WQ4_CHAIN_MAX] = {};
+                int n = 0;
+                g[n].w = L.cout.w; g[n].bias = L.cout.bias; g[n].x16 = m->datt16; g[n].residual = m->dx; g[n].y32 = m->dx;
+                g[n].y16 = m->dxn16; g[n].y16_scale = L.mlp_ln.w; g[n].stats_out = m->dln_stats_a; g[n].dep = -1;
+                const int i_cout = n++;
+                g[n].w = L.fc1.w; g[n].bias = L.fc1_b2; g[n].cvec = L.fc1_c; g[n].x16 = m->dxn16; g[n].y16 = m->dh16;
+                g[n].stats_in = m->dln_stats_a; g[n].stats_groups = groups; g[n].dep = i_cout; g[n].flags = WQ4_EPI_GELU;
+                const int i_fc1 = n++;
+                // fc2 walks K = 4D: split into K pieces on different CTA pairs, chained through their epilogues
+                int64_t fn, fk;
+                wq4_tensor_shape(L.fc2.w, &fn, &fk);
+                const int kst = (int)(fk / 128);
+                int pieces = decode_chain_fc2_pieces();
+                while (pieces > 1 && kst % pieces != 0) pieces--;
+                int i_prev = -1;
+                for (int pc = 0; pc < pieces; pc++) {
+                    g[n].w = L.fc2.w; g[n].bias = pc == 0 ? L.fc2.bias : nullptr; g[n].x16 = m->dh16; g[n].residual = m->dx; g[n].y32 = m->dx;
+                    g[n].dep = i_fc1; g[n].k_stage0 = pc * (kst / pieces); g[n].k_stages = kst / pieces; g[n].edep_plus1 = i_prev + 1;
+                    i_prev = n++;
+                }
+                if (N) {
+                    g[i_prev].y16 = m->dxn16; g[i_prev].y16_scale = N->attn_ln.w; g[i_prev].stats_out = m->dln_stats_b;
+                    g[n].w = N->qkv.w; g[n].bias = N->qkv_b2; g[n].cvec = N->qkv_c; g[n].x16 = m->dxn16; g[n].y32 = m->dqkv;
+                    g[n].stats_in = m->dln_stats_b; g[n].stats_groups = groups; g[n].dep = i_prev;
+                    n++;
+                }
+                CHK(launch_chain_maybe_split(g, n, R, m->dchain_ctr, tm, st));
+            }
+        }
+    }
+    for (size_t l = 0; l < (chained ? (size_t)0 : m->dec.size()); l++) {
         DecLayer &L = m->dec[l];
         __half *sk = m->self_k + l * (size_t)KB * ctx * D, *sv = m->self_v + l * (size_t)KB * ctx * D;
         const __half *ck = m->cross_kv + l * (size_t)M * 2 * D;
