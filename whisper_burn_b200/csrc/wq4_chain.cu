@@ -166,6 +166,19 @@ __device__ __forceinline__ void dep_wait(const unsigned *ctr, unsigned want, int
     __syncwarp();
 }
 
+// The same for a count that is known to be there already: straight to the acquiring load (loops only if it is not).
+__device__ __forceinline__ void dep_acquire(const unsigned *ctr, unsigned want, int lane, volatile int *cta_abort, int *dev_err, int code)
+{
+    if (lane == 0) {
+        unsigned spins = 0;
+        while (ld_acquire_gpu_u32(ctr) < want) {
+            __nanosleep(100);
+            if (++spins > (1u << 22) || *cta_abort) { *cta_abort = 1; atomicCAS(dev_err, 0, code); break; }
+        }
+    }
+    __syncwarp();
+}
+
 // which problem a tile of the launch's list belongs to
 __device__ __forceinline__ int prob_of(const ChainParams &p, int g)
 {
@@ -573,11 +586,19 @@ q4_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ 
             const bool early_res = res && P.dep < 0 && P.edep < 0;
             if (early_res) load_res(eh * 32);
             const float2 *stat = stat_all + (ft & 1u) * TILE_M;
-            if (fold) mbar_wait(bar_stat_full(ft & 1u), (ft >> 1) & 1u, cta_abort, p.dev_err, 215);
+            // This warp's own acquire of the producer's stores (one acquiring load of a counter that is already complete: no
+            // polling).  A folding tile takes it as soon as its statistics are ready -- the statistics warp has seen the row
+            // block complete -- so the L2 round trip runs under the tile's MMAs; other tiles take it once the accumulator is
+            // ready (their X producer has seen the row block complete).
+            bool acquired = P.dep < 0;
+            if (fold) {
+                mbar_wait(bar_stat_full(ft & 1u), (ft >> 1) & 1u, cta_abort, p.dev_err, 215);
+                if (P.dep >= 0) { dep_acquire(p.counters + (size_t)(P.dep * p.mtiles + rb) * kCtrStride, (unsigned)P.dep_count, lane, cta_abort, p.dev_err, 212); acquired = true; }
+            }
             if (warp == 12) CH_TL(it, 5);
             mbar_wait(bar_acc_full(ab), (it / ACC) & 1u, cta_abort, p.dev_err, 208);
             tc_fence_after();
-            if (P.dep >= 0) dep_wait(p.counters + (size_t)(P.dep * p.mtiles + rb) * kCtrStride, (unsigned)P.dep_count, lane, cta_abort, p.dev_err, 212);
+            if (!acquired) dep_acquire(p.counters + (size_t)(P.dep * p.mtiles + rb) * kCtrStride, (unsigned)P.dep_count, lane, cta_abort, p.dev_err, 212);
             if (P.edep >= 0) dep_wait(p.counters + (size_t)(P.edep * p.mtiles + rb) * kCtrStride, (unsigned)P.edep_count, lane, cta_abort, p.dev_err, 216);
             if (res && !early_res) load_res(eh * 32);
             if (warp == 12) CH_TL(it, 6);
