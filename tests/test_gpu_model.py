@@ -296,3 +296,39 @@ def test_per_op_decode_without_skinny_kernel_in_child_process():
                         "every_batch_size and (11 or 26)"], env=env, capture_output=True, text=True, timeout=900)
     print(r.stdout[-600:], r.stderr[-600:])
     assert r.returncode == 0 and "2 passed" in r.stdout
+
+
+def _child(env_extra, kexpr, timeout=900):
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    env = dict(os.environ, **env_extra)
+    r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-q", "-x", "-m", "gpu", "-k", kexpr],
+                       env=env, capture_output=True, text=True, timeout=timeout)
+    print(r.stdout[-600:], r.stderr[-600:])
+    return r
+
+
+@pytest.mark.parametrize("env", [{"WQ4_CHAIN": "0"}, {"WQ4_CHAIN_SPLITK": "1"}, {"WQ4_CHAIN_TILE_M": "192"}])
+def test_encoder_arms_in_child_process(env):
+    """The encoder's A/B arms (settings are read once per process): one launch per GEMM and LayerNorm (WQ4_CHAIN=0, the
+    round-1 path), the chained launch with fc2 split along K through an epilogue dependency, and the 192-row tile of the
+    chained launch at 1500 rows -- each against the oracle and the Hugging Face outputs."""
+    import os
+    if any(os.environ.get(k) for k in ("WQ4_CHAIN", "WQ4_CHAIN_SPLITK", "WQ4_CHAIN_TILE_M", "WQ4_DECODE_CHAIN")):
+        pytest.skip("already inside a child")
+    r = _child(env, "encoder_matches_oracle or hf_second_opinion")
+    assert r.returncode == 0 and "2 passed" in r.stdout
+
+
+@pytest.mark.parametrize("mode", ["1", "2"])
+def test_chained_decode_steps_in_child_process(mode):
+    """WQ4_DECODE_CHAIN=1 / 2: decode steps of 17+ clips on the chain kernel (LayerNorm folded into the consumer's epilogue;
+    one launch per linear / one launch per group of linears), off by default because measured slower; batches 19 and 26
+    against the oracle."""
+    import os
+    if any(os.environ.get(k) for k in ("WQ4_CHAIN", "WQ4_CHAIN_SPLITK", "WQ4_CHAIN_TILE_M", "WQ4_DECODE_CHAIN")):
+        pytest.skip("already inside a child")
+    r = _child({"WQ4_DECODE_CHAIN": mode, "WQ4_DECODE_CHAIN_FC2": "2"}, "every_batch_size and (19 or 26)")
+    assert r.returncode == 0 and "2 passed" in r.stdout
