@@ -721,10 +721,7 @@ int32_t launch_chain(const ChainMaps &maps, const ChainParams &p, int device, cu
         if (device >= 0 && device < 64) attr_done[device] = true;
     }
     int pairs = wq4_sm_count(device) / 2;
-    if (p.total_tiles < pairs) pairs = p.total_tiles;
-    if (pairs < 1) return WQ4_OK;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(2 * pairs), 1, 1);
     cfg.blockDim = dim3(kThreadsC, 1, 1);
     cfg.dynamicSmemBytes = L::alloc;
     cfg.stream = stream;
@@ -733,6 +730,25 @@ int32_t launch_chain(const ChainMaps &maps, const ChainParams &p, int device, cu
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    // Tiles wait for tiles of other CTA pairs, so every launched pair must be resident at once: never launch more pairs
+    // than the device can hold of this kernel (asked once per device; an idle B200 holds one pair per two SMs)
+    static std::atomic<int> max_pairs[64];
+    if (device >= 0 && device < 64) {
+        int mp = max_pairs[device].load();
+        if (mp == 0) {
+            cfg.gridDim = dim3((unsigned)(2 * pairs), 1, 1);
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n < 1) { cudaGetLastError(); n = pairs; }
+            mp = n;
+            max_pairs[device].store(mp);
+        }
+        if (pairs > mp) pairs = mp;
+    }
+    if (p.total_tiles < pairs) pairs = p.total_tiles;
+    if (pairs < 1) return WQ4_OK;
+    cfg.gridDim = dim3((unsigned)(2 * pairs), 1, 1);
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
