@@ -19,12 +19,19 @@
 //         LN(x) . W^T = r * ( (gamma o x) . W^T  -  mu * c )  +  b',      c[n] = sum_k W[n,k] gamma[k],
 //                                                                         b'[n] = bias[n] + sum_k W[n,k] beta[k]
 //     (mu, r = row mean and 1/sqrt(var + 1e-5), src/model/layers.rs:23-31).  The producer GEMM (out-proj / fc2) writes the
-//     f32 residual stream x, the f16 operand gamma o x of the consumer, and per 32-column group the row partials
-//     (sum, sum of squares); the consumer's epilogue warps combine the D/32 partials of their rows in a fixed order
-//     (Chan's parallel-variance update: deterministic, no cancellation of the global mean) while the tile's MMAs run, and
-//     apply r, mu, c, b' to the accumulator.  c and b' are computed once at load with the f32 GEMV kernel.
+//     f32 residual stream x, the f16 operand gamma o x of the consumer, and per 128-column group (one CTA's columns; its
+//     four quarter warps add their 32-column sums in a fixed order through shared memory) the row partials (sum, sum of
+//     squares).  In the consumer CTA the otherwise idle TMEM-allocator warp turns the D/128 partials of a tile's rows into
+//     (mu, r) -- sum (x-mu)^2 = sum_g [q_g - s_g^2/128] + 128 sum_g (s_g/128 - mu)^2: independent terms, deterministic, no
+//     cancellation of a large row mean -- into a double-buffered shared-memory table while the tile's MMAs run, and the
+//     epilogue applies r, mu, c, b' to the accumulator.  c and b' are computed once at load with the f32 GEMV kernel.
 //     No LayerNorm launch and no normalised copy of x exist inside an encoder block any more.
-// Launches per encoder block: 2 (chain + attention) instead of 7.
+//   * The epilogue runs on eight warps (two per TMEM lane quarter) in the transposed domain: a 32 x 32 chunk goes through a
+//     per-warp shared-memory scratch so that fold, bias, GELU, residual, statistics and stores work on float4 of four
+//     consecutive columns (128-byte row segments per store instead of 32 scalar stores per lane).
+//   * A problem may cover a K range of its weight (k_stage0, k_stages) and wait, in its EPILOGUE only, for another problem's
+//     row block (edep): split-K as two problems on different pairs, the second adding to what the first wrote in place.
+// Launches per encoder block: 2 (chain + attention) instead of 7.  Measured numbers and what bounds it: DESIGN.md 4.1b.
 //
 // Roofline: tensor cores; algorithmic work = sum over the problems of 2*rows*N*K flop per launch.
 #include <cuda.h>
@@ -84,7 +91,7 @@ struct ChainProb {
     float *y32;               // f32 [rows][ld] or null
     __half *y16;              // f16 [rows][ld] or null
     const float *y16_scale;   // [n]: gamma of the consumer's LayerNorm, multiplied into y16; null = 1
-    float2 *stats_out;        // [n/32][rows] (sum, sum of squares) or null
+    float2 *stats_out;        // [n/128][rows] (sum, sum of squares) or null
     const float2 *stats_in;   // fold: partials of the rows of X
     int stats_groups;
     int kbp, n, npairs, kst, ks0, ld;     // kst K stages starting at stage ks0 (split-K halves of one weight are two problems)

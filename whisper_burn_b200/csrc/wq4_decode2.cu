@@ -15,17 +15,18 @@
 //   phase B  (sum of the partials + bias + x) -> LN2 -> cross-q_h -> cross-attention of head h -> partial of cross-out
 //   phase C  (sum ...) -> LN3 -> fc1 rows of the cluster's F-slice + GELU [cluster exchange] -> fc2 restricted to those
 //            256 input columns: a partial D-vector per cluster
-// so the only grid-wide exchange is "H partial vectors -> everyone", three times per layer.  The partial sums are added
-// in a fixed order (deterministic, bit-identical run to run).  To keep the exchange cheap each CTA of a cluster sums the
-// partials of ITS 1/CS of the columns only (17 KB out of L2 instead of 102 KB; chip-wide 2 MB instead of 12 MB, which
-// alone would take ~1 us at the L2's ~6 KB/clk) and pushes the slice to its cluster peers through distributed shared
-// memory; every CTA then holds the whole residual vector x in shared memory for the life of the kernel.
+// so the only grid-wide exchange is "H partial vectors -> everyone", three times per layer.  The partial vectors are summed by
+// the memory system: every CTA adds its slice of its cluster's partial into one vector of 64-bit fixed-point accumulators
+// (red.global.add.u64 of value * 2^28: integer addition is associative, so the result is bit-identical run to run), and
+// after the grid barrier every CTA reads the D accumulators (10 KB out of L2, one round trip) and keeps the whole residual
+// vector x in shared memory for the life of the kernel.  (First form of this kernel: H f32 partial vectors in global
+// memory, each CTA summing 1/CS of the columns and broadcasting them through distributed shared memory: +2 us per phase.)
 //
 // Weights never wait for the activations: a layer's three weight slabs of a CTA (31 + 16 + 62 KB at Large-V3) and its
 // share of the head's cross K/V (64 KB) are fetched by cp.async.bulk into dedicated shared-memory buffers ONE LAYER AHEAD
 // (each buffer is refilled as soon as its phase has consumed it), so by the time a phase needs them they are resident
-// and the dependent chain of a phase is: poll -> 17 KB of L2 reads -> DSMEM exchange -> LayerNorm -> GEMV from shared
-// memory -> DSMEM exchange -> attention from shared memory / registers -> DSMEM exchange -> GEMV -> store + release.
+// and the dependent chain of a phase is: poll -> 10 KB of L2 reads -> LayerNorm -> GEMV from shared memory -> DSMEM
+// exchange -> attention from shared memory / registers -> DSMEM exchange -> GEMV -> fixed-point reductions + release.
 //
 // Decode layout (built at load, wq4m_dec2_create): per (layer, phase, CTA) one contiguous slab
 //   [nib1: rows1 x kb1 uint4, row-major][scl1: rows1 x kb1 f16][nib2: rows2 x kb2 uint4][scl2]
@@ -33,7 +34,8 @@
 // GEMV mapping: G lanes of a warp share one weight row and split its k-blocks (consecutive lanes read consecutive
 // 16-byte blocks: conflict-free), the activation vector sits in shared memory padded by 4 floats per 32 so that the
 // eight lanes of a quarter-warp read eight different bank groups; the row sum is a shuffle reduction (no shared-memory
-// round trip, no __syncthreads inside a GEMV).  Arithmetic is f32 throughout ((nib - 8) exact, one scale multiply per block).
+// round trip, no __syncthreads inside a GEMV).  Activations are f16 in shared memory and the products run on the
+// mixed-precision FMA (fma.rn.f32.f16: (nib - 8) exact in f16, f32 accumulation, one f32 scale multiply per block).
 #include <atomic>
 #include <float.h>
 #include <stdio.h>
@@ -146,24 +148,6 @@ __device__ __forceinline__ float block_dot32_h(uint4 q, const __half *xh)
         fhfma2(s2, s3, *reinterpret_cast<const uint32_t *>(&h3), xq.w);
     }
     return (s0 + s1) + (s2 + s3);
-}
-
-// (f32 form, kept for reference / the logits stage)
-// sum_k (nib - 8) * x[k] over one 32-weight block; xp = padded activation pointer of the block (16-byte aligned)
-__device__ __forceinline__ float block_dot32(uint4 q, const float *xp)
-{
-    float s0 = 0.0f, s1 = 0.0f;
-    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-        float f[8];
-        word_f32(w[c], f);
-        const float4 xa = *reinterpret_cast<const float4 *>(xp + c * 8);
-        const float4 xb = *reinterpret_cast<const float4 *>(xp + c * 8 + 4);
-        s0 = fmaf(f[0], xa.x, s0); s0 = fmaf(f[1], xa.y, s0); s0 = fmaf(f[2], xa.z, s0); s0 = fmaf(f[3], xa.w, s0);
-        s1 = fmaf(f[4], xb.x, s1); s1 = fmaf(f[5], xb.y, s1); s1 = fmaf(f[6], xb.z, s1); s1 = fmaf(f[7], xb.w, s1);
-    }
-    return s0 + s1;
 }
 
 // One GEMV job of this CTA out of shared memory: y[r] = sum_k W[r][k] x[k], r < rows.  G lanes per row (power of two).
