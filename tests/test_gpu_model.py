@@ -60,6 +60,23 @@ def test_encoder_matches_oracle(tiny):
     assert e < 5e-3
 
 
+@pytest.mark.parametrize("t_enc,batch", [(64, 2), (100, 1), (100, 3), (129, 1), (193, 2), (256, 1), (300, 3)])
+def test_encoder_ragged_row_counts(t_enc, batch):
+    """Row counts around the chained launch's 128-row blocks (rows = t_enc x batch: exactly one block, one row more, ragged
+    last blocks, several clips per block) and below its threshold (100 rows: one launch per GEMM), against the oracle."""
+    cfg = wn.tiny_config(d=256, heads=4, enc_layers=2, dec_layers=1, n_audio_ctx=t_enc)
+    blob = wn.state_to_gguf(wn.random_state(cfg, seed=31, n_vocab=300))
+    oracle = wn.WhisperOracle(blob, cfg)
+    model = wb.load_whisper_from_gguf(blob, _cfg_pair(cfg), DEV)
+    mel = wn.synthetic_mel(batch, cfg.n_mels, 2 * t_enc, seed=32 + t_enc)
+    want = oracle.encode(mel)
+    got = model.encode(torch.from_numpy(mel).to(DEV)).cpu().numpy()
+    assert got.shape == want.shape == (batch, t_enc, 256)
+    e = rel_err(got, want)
+    print(f"t_enc {t_enc} batch {batch}: encoder rel err {e:.3e}")
+    assert e < 5e-3
+
+
 def test_encoder_short_context_reference_written_gguf(golden_dir):
     """Loads the GGUF the reference's converter wrote (tests/golden) and encodes: T_enc = 32 (one
     partial attention tile), vocab 64."""
