@@ -29,9 +29,9 @@ class Wq4Error(RuntimeError):
         self.message = message
 
 
-def build(verbose: bool = False) -> Path:
-    """Compile the CUDA sources for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
-    r = subprocess.run([str(_PKG / "csrc" / "build.sh")], capture_output=True, text=True)
+def build(verbose: bool = False, clean: bool = False) -> Path:
+    """Compile the CUDA sources for sm_100a in-tree (nvcc cross-compiles without a GPU).  clean=True rebuilds every object."""
+    r = subprocess.run([str(_PKG / "csrc" / "build.sh")] + (["--clean"] if clean else []), capture_output=True, text=True)
     if verbose or r.returncode != 0:
         print(r.stdout[-4000:])
         print(r.stderr[-8000:])

@@ -10,6 +10,8 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo
        -Xcompiler -fPIC,-fvisibility=hidden,-Wall
        --expt-relaxed-constexpr -Xptxas -v)
 SRCS=(wq4_api wq4_tensor wq4_gemv wq4_skinny wq4_gemm wq4_gemm2 wq4_chain wq4_model_kernels wq4_decode wq4_decode2 wq4_attn wq4_mel wq4_whisper wq4_noalloc)
+# --clean: forget every object first (what __graft_entry__.build() does: the check must prove the sources compile)
+if [ "${1:-}" = "--clean" ]; then shift; rm -rf "$OBJ"; fi
 mkdir -p "$OBJ"
 newest_hdr=$(ls -t "$HERE"/*.cuh "$HERE"/../../include/*.h "$HERE"/build.sh | head -1)
 pids=()

@@ -319,7 +319,7 @@ int32_t wq4_linear_plan(const wq4_tensor *w, int64_t rows, uint32_t flags, int32
         if (tile_m) *tile_m = 16;      /* weight rows per CTA of the skinny kernel */
         return 2;
     }
-    if (tile_m) *tile_m = wq4_gemm_impl() == 2 ? wq4_pick_tile_m2(rows, w->np_alloc / 2) : wq4_pick_tile_m(rows, w->np);
+    if (tile_m) *tile_m = wq4_gemm_impl() == 2 ? wq4_pick_tile_m2(rows, w->np_alloc / 2, w->device) : wq4_pick_tile_m(rows, w->np);
     return 1;
 }
 
@@ -353,7 +353,7 @@ int32_t wq4_linear_forward_ex(const wq4_tensor *w, const float *bias_dev, const 
     if ((flags & WQ4_FORCE_GEMV) && rows <= 8 && x_f32_dev) gemv = true;
     if (gemv) return wq4_launch_gemv(a);
     if (use_skinny(w, rows, flags)) return wq4_launch_skinny(a, nullptr);
-    if (wq4_gemm_impl() == 2) return wq4_launch_gemm2_q4(a, wq4_pick_tile_m2(rows, w->np_alloc / 2));
+    if (wq4_gemm_impl() == 2) return wq4_launch_gemm2_q4(a, wq4_pick_tile_m2(rows, w->np_alloc / 2, w->device));
     return wq4_launch_gemm_q4(a, wq4_pick_tile_m(rows, w->np));
 }
 

@@ -132,7 +132,7 @@ bool wq4_skinny_supported(const wq4_tensor *w, int64_t rows);   // matrix-mode w
 int wq4_pick_tile_m(int64_t rows, int64_t np);
 // second-generation Q4 GEMM (CTA pair, A operand in tensor memory; wq4_gemm2.cu)
 int32_t wq4_launch_gemm2_q4(const LinearArgs &a, int tile_m);
-int wq4_pick_tile_m2(int64_t rows, int64_t npairs);
+int wq4_pick_tile_m2(int64_t rows, int64_t npairs, int device);
 int wq4_gemm_impl();   // 2 (default) or 1 (WQ4_GEMM_IMPL=1: first-generation kernel, kept for A/B runs)
 int wq4_gemm_cluster_size(int64_t np);
 

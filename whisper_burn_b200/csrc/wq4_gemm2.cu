@@ -529,7 +529,7 @@ extern "C" WQ4_API void wq4_debug_gemm_timeline(void *dev_ptr) { g_gemm_timeline
 // Row-tile heuristic for the CTA-pair kernel.  Per pair tile the time is ~ max(MMA, dequant) per K stage plus a
 // fixed fill/drain part; cost model in units of "activation rows": waves * (max(tile_m, 150) + 48), fitted to
 // profiles/r01 (per pair tile at K = 1280: 6.1 / 7.3 / 10.6 us for 128 / 192 / 256 rows).
-int wq4_pick_tile_m2(int64_t rows, int64_t npairs)
+int wq4_pick_tile_m2(int64_t rows, int64_t npairs, int device)
 {
     static int forced = -1;
     if (forced < 0) {
@@ -540,7 +540,7 @@ int wq4_pick_tile_m2(int64_t rows, int64_t npairs)
     // One row tile or less: such launches are a single serial walk over K per CTA pair, and a K stage costs
     // 8 x (36 + TILE_M/2) clk of MMA issue, so the narrowest tile is the fastest (decode steps of 17..64 clips)
     if (rows <= 64) return 64;
-    const int pairs = 74;
+    const int pairs = wq4_sm_count(device) / 2 > 0 ? wq4_sm_count(device) / 2 : 74;   // CTA pairs that run at once
     int best = 64;
     double best_cost = 1e30;
     const int cands[4] = {256, 192, 128, 64};
