@@ -255,6 +255,27 @@ def test_conv1d_matches_reference_layer(b, cin, t_in, cout, stride):  # layers.r
     assert rel_err(out_g, want_g) < REL_TOL
 
 
+@pytest.mark.parametrize("b,cin,t_in,cout,stride", [(2, 80, 3000, 1024, 1), (1, 1280, 3000, 1280, 2)])
+def test_conv1d_against_torch_conv1d(b, cin, t_in, cout, stride):
+    """Second opinion for the row the reference leaves unpinned (layers.rs:77-132 has no test): the CUDA stem against
+    torch.nn.functional.conv1d in f32 (TF32 off) on the same inputs, an implementation independent of oracle/."""
+    rng = np.random.default_rng(7 + cin)
+    x = t(rng.standard_normal((b, cin, t_in)).astype(np.float32))
+    w = (rng.standard_normal((cout, cin, 3)) * (1.0 / np.sqrt(3 * cin))).astype(np.float32)
+    bias = rng.standard_normal(cout).astype(np.float32) * 0.1
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        want = torch.nn.functional.conv1d(x, t(w), t(bias), stride=stride, padding=1)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    got = wb.Conv1D(w, bias, device=DEV).forward(x, 1, stride)
+    assert got.shape == want.shape
+    e = float((got - want).abs().max() / want.abs().max())
+    print("conv1d vs torch rel err", e)
+    assert e < REL_TOL
+
+
 def test_linearity_and_determinism_at_full_size():
     """Size-independent properties at the Large-V3 encoder shape (no oracle needed):
     f(a*x) == a*f(x) for a power of two (exact in floating point), f(0) == bias, and two runs
