@@ -209,7 +209,7 @@ struct EpiTile {
 
 // One 32 x 32 chunk in the transposed domain: lane = rows (i*4 + lane/8), columns nc..nc+3.  Branch-free for a given mode so
 // that the eight row groups overlap (loads first, then arithmetic, predicated stores).
-template <bool FOLD, bool GELU, bool RES, bool Y32, bool Y16, bool STATS>
+template <bool FOLD, bool GELU, bool RES, bool Y32, bool Y16, bool STATS, bool SCALE16 = STATS>
 __device__ __forceinline__ void epi_chunk_t(const float *tr, const float2 *stat, const EpiTile &T, const float4 (&r4)[8],
                                             int tb, int nvalid, int lane, float2 *sp, int qq, int bar_id)
 {
@@ -247,7 +247,9 @@ __device__ __forceinline__ void epi_chunk_t(const float *tr, const float2 *stat,
         const long long o = (long long)(tb + rI) * T.ld + T.nc;
         if constexpr (Y32) { if (ok) *reinterpret_cast<float4 *>(T.y32 + o) = a[i]; }
         if constexpr (Y16) {
-            const __half2 h0 = __floats2half2_rn(a[i].x * T.gs4.x, a[i].y * T.gs4.y), h1 = __floats2half2_rn(a[i].z * T.gs4.z, a[i].w * T.gs4.w);
+            // the f16 copy carries the consumer LayerNorm's gamma only in the residual + statistics mode
+            const __half2 h0 = SCALE16 ? __floats2half2_rn(a[i].x * T.gs4.x, a[i].y * T.gs4.y) : __floats2half2_rn(a[i].x, a[i].y);
+            const __half2 h1 = SCALE16 ? __floats2half2_rn(a[i].z * T.gs4.z, a[i].w * T.gs4.w) : __floats2half2_rn(a[i].z, a[i].w);
             uint2 pk;
             pk.x = *reinterpret_cast<const uint32_t *>(&h0);
             pk.y = *reinterpret_cast<const uint32_t *>(&h1);
@@ -572,9 +574,9 @@ q4_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ 
             int mode = 5;
             if (!fold && !P.gelu && res && P.y32 && P.y16 && P.stats_out) mode = 0;
             else if (!fold && !P.gelu && res && P.y32 && !P.y16 && !P.stats_out) mode = 1;
-            else if (fold && P.gelu && !res && !P.y32 && P.y16 && !P.stats_out) mode = 2;
-            else if (fold && !P.gelu && !res && !P.y32 && P.y16 && !P.stats_out) mode = 3;
-            else if (!fold && !P.gelu && !res && !P.y32 && P.y16 && !P.stats_out) mode = 4;
+            else if (fold && P.gelu && !res && !P.y32 && P.y16 && !P.stats_out && !P.y16_scale) mode = 2;
+            else if (fold && !P.gelu && !res && !P.y32 && P.y16 && !P.stats_out && !P.y16_scale) mode = 3;
+            else if (!fold && !P.gelu && !res && !P.y32 && P.y16 && !P.stats_out && !P.y16_scale) mode = 4;
             else if (fold && !P.gelu && !res && P.y32 && !P.y16 && !P.stats_out) mode = 6;      // decoder q|k|v / cross-q: f32 for the attention kernel
             // the producer's stores (residual stream) are acquired by this warp itself, not only through the
             // X producer -> TMA -> MMA -> accumulator barrier chain
