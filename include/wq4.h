@@ -179,7 +179,9 @@ WQ4_API int32_t wq4_whisper_reserve(wq4_whisper *m, int64_t max_batch);
 WQ4_API int32_t wq4_whisper_info(const wq4_whisper *m, int64_t *d_model, int64_t *ffn, int64_t *vocab,
                                  int64_t *weight_bytes);
 /* mel_dev [batch, n_mels, 2*n_audio_ctx] f32 -> enc_out_dev [batch, n_audio_ctx, D] f32 (may be NULL:
- * the encoder output then only stays inside the model for the decoder). */
+ * the encoder output then only stays inside the model for the decoder).  From the second call per batch size on, everything
+ * after the input transpose is replayed as one CUDA graph on `stream` (not on the legacy default stream, not inside a
+ * caller's own stream capture, where the launches join the caller's graph; WQ4_ENCODE_GRAPH=0 turns it off). */
 WQ4_API int32_t wq4_whisper_encode(wq4_whisper *m, const float *mel_dev, int64_t batch,
                                    float *enc_out_dev, wq4_stream stream);
 /* Greedy transcription of `batch` clips (see wq4_whisper.cu for the prompt modes).

@@ -77,6 +77,24 @@ def test_encoder_ragged_row_counts(t_enc, batch):
     assert e < 5e-3
 
 
+def test_encode_replays_its_graph_with_fresh_inputs():
+    """wq4_whisper_encode captures the encoder into a CUDA graph on the second call per batch size and replays it: different
+    inputs on every call, a larger batch in between (re-reservation drops the graphs of the old workspaces), on a side stream."""
+    cfg = wn.tiny_config(d=256, heads=4, enc_layers=2, dec_layers=1, n_audio_ctx=300)
+    blob = wn.state_to_gguf(wn.random_state(cfg, seed=5, n_vocab=300))
+    oracle = wn.WhisperOracle(blob, cfg)
+    model = wb.load_whisper_from_gguf(blob, _cfg_pair(cfg), DEV)
+    counts = []
+    with torch.cuda.stream(torch.cuda.Stream()):
+        for i, b in enumerate((2, 2, 2, 2, 3, 3, 3, 2, 2, 2)):
+            mel = wn.synthetic_mel(b, cfg.n_mels, 600, seed=40 + i)
+            wb.reset_launch_count()
+            got = model.encode(torch.from_numpy(mel).to(DEV)).cpu().numpy()
+            counts.append(wb.launch_count())
+            assert rel_err(got, oracle.encode(mel)) < 5e-3, i
+    assert counts[2] == counts[3] == counts[9] and counts[2] > 2      # replayed passes report the launches of the graph
+
+
 def test_encoder_short_context_reference_written_gguf(golden_dir):
     """Loads the GGUF the reference's converter wrote (tests/golden) and encodes: T_enc = 32 (one
     partial attention tile), vocab 64."""

@@ -33,6 +33,7 @@ void wq4_count_launch(int n) { g_launches += n; }
 struct ProfRec { int kind; double work; cudaEvent_t e0, e1; };
 static thread_local bool g_prof_on = false;
 static thread_local std::vector<ProfRec> *g_prof = nullptr;
+bool wq4_profile_active() { return g_prof_on; }
 
 WqProfScope::WqProfScope(int kind, double work, cudaStream_t st) : active(false), stream(st)
 {

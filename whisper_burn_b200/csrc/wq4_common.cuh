@@ -62,6 +62,7 @@ struct wq4_conv1d {
 void wq4_set_error(const char *fmt, ...);
 int32_t wq4_cuda_fail(cudaError_t e, const char *what);
 void wq4_count_launch(int n = 1);
+bool wq4_profile_active();              // per-kernel profiler on (bench.py roofline leg): launches must stay individual
 int *wq4_error_flag_ptr(int device);   // device int, sticky, lazily allocated per device
 int wq4_sm_count(int device);
 

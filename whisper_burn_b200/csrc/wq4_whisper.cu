@@ -186,6 +186,10 @@ struct wq4_whisper {
     float2 *ln_stats_a = nullptr, *ln_stats_b = nullptr;   // [D/128][rows] row partials of the residual stream (wq4_chain.cu)
     unsigned *chain_ctr = nullptr;                         // row-block arrival counters of the chain launches, zero between launches
     bool chain_ready = false;
+    // wq4_whisper_encode replays a CUDA graph of the encoder per batch size (first call eager, second call captures): 54
+    // launches per Medium pass become one graph launch on the caller's stream.  call count and exec per batch.
+    struct EncGraph { int calls = 0; cudaGraphExec_t exec = nullptr; int64_t launches = 0; bool failed = false; };
+    std::map<int64_t, EncGraph> enc_graphs;
     float2 *dln_stats_a = nullptr, *dln_stats_b = nullptr; // the same for the decoder's chained steps: [D/128][max_batch * max_q]
     unsigned *dchain_ctr = nullptr;
     int64_t Cp1 = 0, Tp1 = 0, Tp2 = 0;
@@ -533,6 +537,8 @@ int32_t reserve(wq4_whisper *m, int64_t B)
         if (m->h_next) { cudaFreeHost(m->h_next); m->h_next = nullptr; }
         m->max_batch = 0;
         m->kv_batch = 0;
+        for (auto &kv : m->enc_graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+        m->enc_graphs.clear();            // the graphs hold the old workspace pointers
     }
     m->Cp1 = (m->cfg.n_mels + 7) / 8 * 8;
     m->Tp1 = m->T_mel + 2;
@@ -642,12 +648,17 @@ static bool use_skinny_step()
 }
 
 // WhisperEncoder::forward (encoder.rs:87-115) for B clips; mel_dev [B, n_mels, 3000] f32.
-int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
+int32_t encode_front(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
+{
+    // mel -> time-major f16 with one zero row before/after each clip (padding 1, layers.rs:83-90): the only kernel that
+    // reads a caller pointer
+    return wq4m_mel_transpose(mel_dev, m->mel_t16, B, m->cfg.n_mels, m->T_mel, m->Cp1, m->Tp1, 1, st);
+}
+
+int32_t encode_body(wq4_whisper *m, int64_t B, cudaStream_t st)
 {
     const int64_t D = m->D, T = m->T_enc, M = B * T;
     const wq4_whisper_config &c = m->cfg;
-    // mel -> time-major f16 with one zero row before/after each clip (padding 1, layers.rs:83-90)
-    CHK(wq4m_mel_transpose(mel_dev, m->mel_t16, B, c.n_mels, m->T_mel, m->Cp1, m->Tp1, 1, st));
     // conv1 (k=3, p=1, s=1) + GELU -> h1 [B][3002][D] f16, rows 1..3000 (encoder.rs:89-90)
     DenseGemmArgs a = {};
     a.w16 = m->conv1->w16; a.x16 = m->mel_t16; a.bias = m->conv1->bias; a.residual = nullptr;
@@ -723,6 +734,49 @@ int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
         CHK(lin16(L.fc2, m->ffn16, m->x, nullptr, m->x, M, 0, st));        // residual + ffn
     }
     return wq4m_layernorm(m->x, m->ln_post.w, m->ln_post.b, m->enc32, m->enc16, M, D, st);   // encoder.rs:114
+}
+
+int32_t encode(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
+{
+    CHK(encode_front(m, mel_dev, B, st));
+    return encode_body(m, B, st);
+}
+
+// WhisperModel::encode through the C ABI: everything after the mel transpose only touches model-owned buffers, so it is
+// captured once per batch size into a CUDA graph (on the second call: the first one runs eagerly and sets up function
+// attributes / occupancy queries / the error flag) and replayed -- one graph launch instead of ~54 kernel launches per
+// Medium pass from the host.  Not used on the legacy default stream, inside a caller's own capture (the launches then go
+// into the caller's graph), while the per-kernel profiler is on, or with WQ4_ENCODE_GRAPH=0.
+int32_t encode_graphed(wq4_whisper *m, const float *mel_dev, int64_t B, cudaStream_t st)
+{
+    static const bool on = [] { const char *e = getenv("WQ4_ENCODE_GRAPH"); return !(e && atoi(e) == 0); }();
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    bool plain = !on || st == nullptr || st == cudaStreamLegacy || st == cudaStreamPerThread || wq4_profile_active();
+    if (!plain && (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)) { cudaGetLastError(); plain = true; }
+    if (plain) return encode(m, mel_dev, B, st);
+    wq4_whisper::EncGraph &g = m->enc_graphs[B];
+    if (g.failed) return encode(m, mel_dev, B, st);
+    if (g.calls++ == 0) return encode(m, mel_dev, B, st);
+    if (!g.exec) {
+        const int64_t before = wq4_launch_count();
+        cudaGraph_t graph = nullptr;
+        if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); g.failed = true; return encode(m, mel_dev, B, st); }
+        const int32_t rc = encode_body(m, B, st);
+        const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        g.launches = wq4_launch_count() - before;
+        wq4_count_launch(-(int)g.launches);                         // recorded into the graph, not launched
+        if (rc != WQ4_OK || ce != cudaSuccess || !graph || cudaGraphInstantiate(&g.exec, graph, 0) != cudaSuccess) {
+            cudaGetLastError();
+            if (graph) cudaGraphDestroy(graph);
+            g.exec = nullptr; g.failed = true;
+            return rc != WQ4_OK ? rc : encode(m, mel_dev, B, st);
+        }
+        cudaGraphDestroy(graph);
+    }
+    CHK(encode_front(m, mel_dev, B, st));
+    WQ4_CUDA(cudaGraphLaunch(g.exec, st));
+    wq4_count_launch((int)g.launches);
+    return WQ4_OK;
 }
 
 // Cross-attention K/V for every decoder layer from the encoder output (attention.rs:185-186):
@@ -1069,6 +1123,7 @@ int32_t wq4_whisper_destroy(wq4_whisper *m)
     }
     wq4_conv1d_destroy(m->conv1);
     wq4_conv1d_destroy(m->conv2);
+    for (auto &kv : m->enc_graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
     for (void *p : m->owned) cudaFree(p);
     for (void *p : m->ws_owned) cudaFree(p);
     if (m->h_next) cudaFreeHost(m->h_next);
@@ -1100,7 +1155,7 @@ int32_t wq4_whisper_encode(wq4_whisper *m, const float *mel_dev, int64_t batch, 
     CHK(reserve(m, batch));
     if (batch > m->max_batch) { wq4_set_error("wq4_whisper_encode: batch %lld exceeds the reserved %lld", (long long)batch, (long long)m->max_batch); return WQ4_ERR_INVALID; }
     cudaStream_t st = (cudaStream_t)stream;
-    CHK(encode(m, mel_dev, batch, st));
+    CHK(encode_graphed(m, mel_dev, batch, st));
     if (enc_out_dev)
         WQ4_CUDA(cudaMemcpyAsync(enc_out_dev, m->enc32, (size_t)batch * m->T_enc * m->D * 4, cudaMemcpyDeviceToDevice, st));
     return WQ4_OK;
