@@ -32,7 +32,8 @@ def reference(qkv, B, T, D, H):
     return o.permute(0, 2, 1, 3).reshape(B * T, D)
 
 
-@pytest.mark.parametrize("B,T,H", [(2, 1500, 4), (1, 32, 2), (1, 128, 1), (1, 129, 2), (1, 1, 1), (3, 300, 20), (1, 257, 3)])
+@pytest.mark.parametrize("B,T,H", [(2, 1500, 4), (1, 32, 2), (1, 128, 1), (1, 129, 2), (1, 1, 1), (3, 300, 20), (1, 257, 3),
+                                   (1, 1500, 16), (1, 1500, 20), (1, 193, 2)])
 @pytest.mark.parametrize("spread", [1.0, 4.0])
 def test_attention_matches_sdpa(B, T, H, spread):
     D = H * 64
@@ -54,3 +55,4 @@ def test_attention_rows_are_convex_combinations():
     qkv[:, 2 * D:] = 1.0
     got = run_attention(qkv, B, T, D, H).float()
     assert float((got - 1.0).abs().max()) < 2e-3
+
