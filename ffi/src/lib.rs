@@ -108,6 +108,16 @@ impl Q4FFN {
     pub fn workspace_bytes(&self, b: usize, m: usize) -> usize {
         unsafe { sys::wq4_ffn_workspace_bytes(self.fc1.weights.raw, self.fc2.weights.raw, b as i64, m as i64) }
     }
+    /// No counterpart in the reference: `forward` for b*m <= 8 rows and a hidden width <= 8192 with the hidden block in a
+    /// static device array of the library -- no workspace, no device allocation (usable under CUDA graph capture).
+    /// Calls on one GPU share that array: do not overlap two of them on unordered streams.
+    pub fn forward_static(&self, x_dev: *const f32, dims: [usize; 3], y_dev: *mut f32, stream: sys::wq4_stream) {
+        let [b, m, _k] = dims;
+        expect_ok(unsafe {
+            sys::wq4_ffn_forward_static(self.fc1.weights.raw, self.fc1.bias.unwrap_or(ptr::null()), self.fc2.weights.raw,
+                                        self.fc2.bias.unwrap_or(ptr::null()), x_dev, y_dev, b as i64, m as i64, stream)
+        }, "Q4FFN forward_static");
+    }
 }
 
 /// src/model/layers.rs:61-133: weight `[out, in, k]` f32 (host), bias `[out]` f32 (host).
