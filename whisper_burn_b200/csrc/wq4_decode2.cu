@@ -810,6 +810,18 @@ static void dec2_geometry(Dec2Args &a, int D, int F, int H, int T_enc, int CS)
 
 static size_t dec2_smem_bytes(const Dec2Args &a) { return (size_t)a.off_bufA + a.sA + a.sB + a.sC + up128((size_t)a.kpc * 256); }
 
+// The kernel's dynamic shared-memory limit is a per-device function attribute that both the planner (one query per
+// candidate cluster size, per model) and the launcher change: one cache of the value last set, so that a model planned
+// later with a smaller footprint cannot leave the limit below what an earlier model's step needs.
+static std::atomic<int> g_dec2_smem_attr[64];
+static cudaError_t dec2_set_smem_limit(int device, size_t smem)
+{
+    if (device >= 0 && device < 64 && g_dec2_smem_attr[device].load() == (int)smem) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(decode2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess && device >= 0 && device < 64) g_dec2_smem_attr[device].store((int)smem);
+    return e;
+}
+
 bool wq4m_dec2_supported(int64_t D, int64_t F, int64_t H)
 {
     return D % 64 == 0 && D == H * 64 && F == 4 * D && D <= 4 * kT && H >= 1 && H <= 148;
@@ -829,7 +841,7 @@ int32_t wq4m_dec2_plan(int device, int64_t D, int64_t F, int64_t H, int64_t T_en
         dec2_geometry(g, (int)D, (int)F, (int)H, (int)T_enc, cs);
         const size_t smem = dec2_smem_bytes(g);
         if (smem > 227 * 1024) continue;
-        if (cudaFuncSetAttribute(decode2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (dec2_set_smem_limit(device, smem) != cudaSuccess) { cudaGetLastError(); continue; }
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(cs * H), 1, 1);
         cfg.blockDim = dim3(kT, 1, 1);
@@ -892,11 +904,7 @@ int32_t wq4m_decode2_step(const Dec2Args &a_in, int device, cudaStream_t st)
     Dec2Args a = a_in;
     a.timeline = g_dec2_timeline;
     const size_t smem = dec2_smem_bytes(a);
-    static std::atomic<int> attr_smem[64];
-    if (device < 0 || device >= 64 || attr_smem[device].load() < (int)smem) {
-        WQ4_CUDA(cudaFuncSetAttribute(decode2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        if (device >= 0 && device < 64) attr_smem[device].store((int)smem);
-    }
+    WQ4_CUDA(dec2_set_smem_limit(device, smem));
     WqProfScope prof(WQ4_PROF_GEMV, 0.0, st);
     WQ4_CUDA(cudaMemsetAsync(a.barrier, 0, 2 * sizeof(unsigned), st));
     cudaLaunchConfig_t cfg = {};
