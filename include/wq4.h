@@ -181,7 +181,11 @@ WQ4_API int32_t wq4_whisper_info(const wq4_whisper *m, int64_t *d_model, int64_t
 /* mel_dev [batch, n_mels, 2*n_audio_ctx] f32 -> enc_out_dev [batch, n_audio_ctx, D] f32 (may be NULL:
  * the encoder output then only stays inside the model for the decoder).  From the second call per batch size on, everything
  * after the input transpose is replayed as one CUDA graph on `stream` (not on the legacy default stream, not inside a
- * caller's own stream capture, where the launches join the caller's graph; WQ4_ENCODE_GRAPH=0 turns it off). */
+ * caller's own stream capture, where the launches join the caller's graph; WQ4_ENCODE_GRAPH=0 turns it off).
+ * The encoder's chained GEMM launch and the single-clip decode step are persistent kernels whose CTAs wait for one another
+ * and fill the device: do not run two model calls concurrently on one GPU (different streams or processes); one host thread
+ * and one stream per GPU, as in the reference's inference thread (src/native/inference.rs:31-65).  A wait that cannot be
+ * satisfied ends after a bounded number of polls and raises the sticky device error flag instead of hanging. */
 WQ4_API int32_t wq4_whisper_encode(wq4_whisper *m, const float *mel_dev, int64_t batch,
                                    float *enc_out_dev, wq4_stream stream);
 /* Greedy transcription of `batch` clips (see wq4_whisper.cu for the prompt modes).
