@@ -77,6 +77,15 @@ def test_null_arguments_are_errors_not_crashes():
     assert b"null" in L.wq4_last_error() or len(L.wq4_last_error()) > 0
 
 
+def test_release_build_has_no_overflow_counter_and_static_ffn_limits():
+    L = wb.lib()
+    assert L.wq4_debug_f16_overflow_count(0, 0) == -1          # counter code only with -DWQ4_DEBUG_OVERFLOW
+    mr, mh = C.c_int64(), C.c_int64()
+    L.wq4_ffn_static_limits(C.byref(mr), C.byref(mh))
+    assert (mr.value, mh.value) == (8, 8192)
+    assert L.wq4_ffn_forward_static(None, None, None, None, None, None, 1, 1, None) == 1     # null weights: invalid, no crash
+
+
 def test_product_package_does_not_import_oracle():
     for f in (ROOT / "whisper_burn_b200").rglob("*"):
         if f.suffix in (".py", ".cu", ".cuh", ".cpp", ".h", ".sh"):
