@@ -276,6 +276,27 @@ def test_conv1d_against_torch_conv1d(b, cin, t_in, cout, stride):
     assert e < REL_TOL
 
 
+@pytest.mark.parametrize("rows", [17, 33, 64])
+@pytest.mark.parametrize("n,k", [(1280, 1280), (1280, 5120), (3840, 1280)])
+def test_small_row_counts_one_tile(rows, n, k):
+    """17..64 rows (decode steps of that many clips): one 64-row tile per CTA pair at the Large-V3 decoder shapes, against
+    the oracle and bit-identical run to run."""
+    rng = np.random.default_rng(rows + n + k)
+    qb = q4.quantize_q4_0_converter((rng.standard_normal(n * k) * 0.02).astype(np.float32))
+    bias = rng.standard_normal(n).astype(np.float32) * 0.1
+    lin = wb.Q4Linear(wb.Q4Tensor.from_q4_bytes(qb, [n, k], DEV), t(bias))
+    x = rng.standard_normal((1, rows, k)).astype(np.float32)
+    q4.set_threads(q4.host_cores())
+    want = q4.q4_linear(x, qb, bias, n)
+    tile = __import__("ctypes").c_int32()
+    assert wb.lib().wq4_linear_plan(lin.weights._h, rows, 0, __import__("ctypes").byref(tile)) == 1 and tile.value == 64
+    y1 = lin.forward(t(x))
+    y2 = lin.forward(t(x))
+    y3 = lin.forward(t(x))
+    assert torch.equal(y1, y2) and torch.equal(y1, y3)
+    assert rel_err(y1.cpu().numpy(), want) < REL_TOL
+
+
 def test_linearity_and_determinism_at_full_size():
     """Size-independent properties at the Large-V3 encoder shape (no oracle needed):
     f(a*x) == a*f(x) for a power of two (exact in floating point), f(0) == bias, and two runs
