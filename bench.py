@@ -508,22 +508,29 @@ def run_own(args):
         # loop would do.  The host only blocks on the read-back of step i-2 (buffer reuse) and at the end.
         copy_stream = torch.cuda.Stream(device=dev)
         out_bufs = [out_host, torch.empty_like(out_host).pin_memory()]
-        done = [None, None]
+
+        def e2e_pass(n_steps):
+            done = [None, None]
+            for i in range(n_steps):
+                m = mel_host.to(dev, non_blocking=True)
+                y = model.encode(m)
+                ready = torch.cuda.Event()
+                ready.record(stream)
+                if done[i % 2] is not None:
+                    done[i % 2].synchronize()
+                copy_stream.wait_event(ready)
+                with torch.cuda.stream(copy_stream):
+                    out_bufs[i % 2].copy_(y, non_blocking=True)
+                    y.record_stream(copy_stream)
+                    done[i % 2] = torch.cuda.Event()
+                    done[i % 2].record(copy_stream)
+            torch.cuda.synchronize()
+
+        e2e_pass(min(args.steps, 5))          # untimed: first touch of the second pinned buffer and of the copy stream
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
-        for i in range(args.steps):
-            m = mel_host.to(dev, non_blocking=True)
-            y = model.encode(m)
-            ready = torch.cuda.Event()
-            ready.record(stream)
-            if done[i % 2] is not None:
-                done[i % 2].synchronize()
-            copy_stream.wait_event(ready)
-            with torch.cuda.stream(copy_stream):
-                out_bufs[i % 2].copy_(y, non_blocking=True)
-                y.record_stream(copy_stream)
-                done[i % 2] = torch.cuda.Event()
-                done[i % 2].record(copy_stream)
-        torch.cuda.synchronize()
+        e2e_pass(args.steps)
         dt_e2e = max_over_ranks(time.perf_counter() - t0)
 
         # ---- roofline: per-kernel CUDA-event timing of the same step (instrumented pass)
